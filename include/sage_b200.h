@@ -1,0 +1,113 @@
+/* sage_b200.h - C ABI of libsage_b200.so (sm_100a SageAttention hot path).
+ *
+ * Drop-in boundary for the reference's pybind extensions.  Every entry point takes plain device
+ * pointers, sizes, element strides and a CUDA stream; nothing is allocated by the library and no
+ * torch type crosses the boundary.  Return value: 0 = ok, <0 = invalid argument (message in
+ * sage_last_error()), >0 = cudaError_t of the failing runtime call / launch.
+ *
+ * Reference interfaces replaced (paths relative to /root/reference):
+ *   sage_quant_int8              <- _fused.quant_per_block_int8_cuda (2 overloads),
+ *                                   quant_per_block_int8_fuse_sub_mean_cuda, quant_per_warp_int8_cuda
+ *                                   (csrc/fused/pybind.cpp:23-26, csrc/fused/fused.cu:429-768)
+ *   sage_quant_per_thread_int8   <- triton per_thread_int8 (sageattention/triton/quant_per_thread.py:158-208)
+ *   sage_sub_mean                <- _fused.sub_mean_cuda (csrc/fused/fused.cu:770-848)
+ *   sage_per_channel_fp8         <- _fused.transpose_pad_permute_cuda + scale_fuse_quant_cuda /
+ *                                   mean_scale_fuse_quant_cuda (csrc/fused/fused.cu:850-1083)
+ *   sage_seq_mean                <- torch `k.mean(dim=seq)` / `v.mean(dim=seq)` (sageattention/core.py:612, quant.py:215)
+ *   sage_attn_i8_f16             <- _qattn_sm80.qk_int8_sv_f16_accum_{f32,f16,f16_inst_buf}_attn,
+ *                                   ..._fuse_v_mean_attn (csrc/qattn/pybind_sm80.cpp, qk_int_sv_f16_cuda_sm80.cu:674-1379)
+ *   sage_attn_i8_f8              <- _qattn_sm89.qk_int8_sv_f8_accum_* (7 variants, csrc/qattn/pybind_sm89.cpp)
+ *   sage_prepass_*               <- the whole quantisation prologue of core.py:590-632 / 794-830 fused.
+ */
+#ifndef SAGE_B200_H_
+#define SAGE_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* dtype codes */
+#define SAGE_DTYPE_F16 0
+#define SAGE_DTYPE_BF16 1
+/* QuantGranularity codes, identical to the reference's enum (csrc/qattn/attn_utils.cuh:44-50) */
+#define SAGE_GRAN_PER_BLOCK 1
+#define SAGE_GRAN_PER_WARP 2
+#define SAGE_GRAN_PER_THREAD 3
+
+/* A 4-D activation tensor [B, H, N, D] addressed through element strides, so both of the
+ * reference's layouts ("HND" and "NHD", core.py:585) and transposed views are one code path.
+ * stride_d is always 1 (the reference asserts stride(-1) == 1, core.py:604). */
+typedef struct sage_tensor4 {
+  void* ptr;
+  int64_t stride_b, stride_h, stride_n; /* in elements */
+} sage_tensor4;
+
+const char* sage_last_error(void);
+int sage_version(void);
+
+/* km[b,h,d] = dtype( (sum_n x[b,h,n,d]) * (1/N) ); out is [B,H,D] contiguous, same dtype as x.
+ * Deterministic two-level reduction; workspace of sage_seq_mean_workspace_bytes() bytes. */
+size_t sage_seq_mean_workspace_bytes(int B, int H, int N, int D);
+int sage_seq_mean(sage_tensor4 x, void* out, int B, int H, int N, int D, int dtype, void* workspace,
+                  void* stream);
+
+/* INT8 quantisation of rows in groups of `block` tokens (block in {16,32,64,128}).
+ *   x' = float(x) [- float(mean[b,h,d])] [* sm_scale]   (mean may be NULL; has_sm_scale 0/1)
+ *   amax = max(1e-7, max|x'|); scale = amax/127; code = cvt.rni.sat.s8(x' * (127/amax))
+ * out: int8 tensor (strides given), scale: [B,H,ceil(N/block)] contiguous fp32. */
+int sage_quant_int8(sage_tensor4 x, const void* mean, sage_tensor4 out, float* scale, int B, int H,
+                    int N, int D, int dtype, int block, int has_sm_scale, float sm_scale,
+                    void* stream);
+
+/* Per-thread granularity (the reference's default, Triton arithmetic):
+ *   scale = max|x|/127 + 1e-7 ; code = trunc(x/scale + 0.5*sign)
+ *   is_key = 0: groups {r, r+8, ...} of each `tile`-row block (tile = WARPQ: 16 or 32), 8 scales per tile
+ *   is_key = 1: groups {8i+2c, 8i+2c+1} of each 64-row block, 4 scales per block; x is first
+ *               replaced by dtype(x - mean) when mean != NULL.
+ * scale: [B,H,ceil(N/128)*(128/tile)*8] (query) or [B,H,ceil(N/64)*4] (key). */
+int sage_quant_per_thread_int8(sage_tensor4 x, const void* mean, sage_tensor4 out, float* scale,
+                               int B, int H, int N, int D, int dtype, int is_key, int tile,
+                               void* stream);
+
+/* out(f16)[b,h,n,d] = half( x - mean ) in the input type's packed arithmetic. */
+int sage_sub_mean(sage_tensor4 x, const void* mean, sage_tensor4 out, int B, int H, int N, int D,
+                  int dtype, void* stream);
+
+/* V -> e4m3 [B,H,D,Npad] (Npad = ceil64(N), 16-token permutation of the reference), per-channel
+ * scale [B,H,D] fp32 and (smooth_v) mean [B,H,D] fp32.  v_out strides: (b, h, d) with n contiguous.
+ * workspace: sage_per_channel_fp8_workspace_bytes(). */
+size_t sage_per_channel_fp8_workspace_bytes(int B, int H, int N, int D);
+int sage_per_channel_fp8(sage_tensor4 v, uint8_t* v_out, int64_t vo_stride_b, int64_t vo_stride_h,
+                         int64_t vo_stride_d, float* v_scale, float* v_mean, int B, int H, int N,
+                         int D, int dtype, float scale_max, int smooth_v, void* workspace,
+                         void* stream);
+
+/* Attention kernels.  q8/k8: int8 [B,H,N,D] via strides; scales laid out exactly as the reference
+ * quantizers produce them; o: f16/bf16 via strides; lse: [B,Hq,Nq] fp32 or NULL (base-2, as the
+ * reference kernels return it). */
+typedef struct sage_attn_args {
+  sage_tensor4 q8, k8, v, o;
+  const float* q_scale;
+  const float* k_scale;
+  const float* v_scale; /* fp8: [B,Hkv,D] or NULL */
+  const float* v_mean;  /* [B,Hkv,D] fp32 or NULL */
+  float* lse;           /* or NULL */
+  int B, Hq, Hkv, Nq, Nk, D;
+  int npad_v;      /* fp8: padded kv length of v (multiple of 64); v strides are (b,h,d) rows */
+  int gran;        /* SAGE_GRAN_* */
+  int warp_q;      /* rows per q-scale group for per_warp / per_thread: 16 or 32 */
+  int is_causal;
+  int out_dtype;   /* SAGE_DTYPE_* */
+  float sm_scale;
+} sage_attn_args;
+
+int sage_attn_i8_f16(const sage_attn_args* a, void* stream);
+int sage_attn_i8_f8(const sage_attn_args* a, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SAGE_B200_H_ */

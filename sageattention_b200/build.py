@@ -1,0 +1,73 @@
+"""Build libsage_b200.so (sm_100a only) in-tree with nvcc.
+
+    python -m sageattention_b200.build [--force]
+
+The library has no torch / pybind dependency: it is a plain C-ABI shared object
+(include/sage_b200.h) that the Python layer binds with ctypes.
+"""
+import os
+import shutil
+import subprocess
+import sys
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(PKG, "csrc")
+ROOT = os.path.dirname(PKG)
+LIB = os.path.join(PKG, "libsage_b200.so")
+OBJ = os.path.join(PKG, "csrc", "_obj")
+
+ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
+COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-w", f"-I{os.path.join(ROOT, 'include')}"]
+# (source, extra flags).  prepass.cu is built with --use_fast_math ON PURPOSE: the reference's
+# quantizers are (setup.py:45-54) and bit-exact codes need the same div.approx/.ftz sequences.
+UNITS = [
+    ("capi.cu", []),
+    ("prepass.cu", ["--use_fast_math"]),
+    ("attn_sm100.cu", []),
+]
+
+
+def _nvcc():
+    return shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+
+
+def _deps(src):
+    hdrs = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
+    hdrs.append(os.path.join(ROOT, "include", "sage_b200.h"))
+    return [src] + hdrs
+
+
+def build(force=False, verbose=False):
+    os.makedirs(OBJ, exist_ok=True)
+    objs, rebuilt = [], False
+    procs = []
+    for name, extra in UNITS:
+        src = os.path.join(CSRC, name)
+        obj = os.path.join(OBJ, name + ".o")
+        objs.append(obj)
+        stale = force or not os.path.exists(obj) or any(
+            os.path.getmtime(d) > os.path.getmtime(obj) for d in _deps(src))
+        if stale:
+            cmd = [_nvcc(), "-c", src, "-o", obj] + ARCH + COMMON + extra
+            if verbose:
+                cmd += ["-Xptxas", "-v"]
+            procs.append((name, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+            rebuilt = True
+    for name, p in procs:
+        out, _ = p.communicate()
+        if p.returncode != 0:
+            sys.stderr.write(out)
+            raise RuntimeError(f"nvcc failed on {name}")
+        if verbose:
+            print(out)
+    if rebuilt or not os.path.exists(LIB):
+        cmd = [_nvcc(), "-shared", "-o", LIB] + objs + ARCH
+        p = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        if p.returncode != 0:
+            sys.stderr.write(p.stdout)
+            raise RuntimeError("link failed")
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
