@@ -57,10 +57,11 @@ int sage_seq_mean(sage_tensor4 x, void* out, int B, int H, int N, int D, int dty
 /* INT8 quantisation of rows in groups of `block` tokens (block in {16,32,64,128}).
  *   x' = float(x) [- float(mean[b,h,d])] [* sm_scale]   (mean may be NULL; has_sm_scale 0/1)
  *   amax = max(1e-7, max|x'|); scale = amax/127; code = cvt.rni.sat.s8(x' * (127/amax))
- * out: int8 tensor (strides given), scale: [B,H,ceil(N/block)] contiguous fp32. */
+ * out: int8 tensor (strides given), scale: [B,H,scale_per_bh] contiguous fp32 with
+ * scale_per_bh >= ceil(N/block) (per_warp_int8 allocates ceil(N/BLKQ)*(BLKQ/WARPQ), quant.py:170). */
 int sage_quant_int8(sage_tensor4 x, const void* mean, sage_tensor4 out, float* scale, int B, int H,
-                    int N, int D, int dtype, int block, int has_sm_scale, float sm_scale,
-                    void* stream);
+                    int N, int D, int dtype, int block, int scale_per_bh, int has_sm_scale,
+                    float sm_scale, void* stream);
 
 /* Per-thread granularity (the reference's default, Triton arithmetic):
  *   scale = max|x|/127 + 1e-7 ; code = trunc(x/scale + 0.5*sign)
@@ -76,13 +77,16 @@ int sage_quant_per_thread_int8(sage_tensor4 x, const void* mean, sage_tensor4 ou
 int sage_sub_mean(sage_tensor4 x, const void* mean, sage_tensor4 out, int B, int H, int N, int D,
                   int dtype, void* stream);
 
-/* V -> e4m3 [B,H,D,Npad] (Npad = ceil64(N), 16-token permutation of the reference), per-channel
- * scale [B,H,D] fp32 and (smooth_v) mean [B,H,D] fp32.  v_out strides: (b, h, d) with n contiguous.
+/* V -> e4m3 [B,H,D,Npad] (16-token permutation of the reference), per-channel scale [B,H,D] fp32
+ * and (smooth_v) mean [B,H,D] fp32.  v_out strides: (b, h, d) with n contiguous.
+ * n_stat >= N is the token count the reference kernel would see: core.py:822-828 zero-pads V to a
+ * multiple of 128 before quantising, so Npad = ceil64(n_stat) and the smooth_v mean divides by
+ * ceil16(n_stat); rows in [N, n_stat) are treated as zeros without being materialised.
  * workspace: sage_per_channel_fp8_workspace_bytes(). */
 size_t sage_per_channel_fp8_workspace_bytes(int B, int H, int N, int D);
 int sage_per_channel_fp8(sage_tensor4 v, uint8_t* v_out, int64_t vo_stride_b, int64_t vo_stride_h,
                          int64_t vo_stride_d, float* v_scale, float* v_mean, int B, int H, int N,
-                         int D, int dtype, float scale_max, int smooth_v, void* workspace,
+                         int n_stat, int D, int dtype, float scale_max, int smooth_v, void* workspace,
                          void* stream);
 
 /* Attention kernels.  q8/k8: int8 [B,H,N,D] via strides; scales laid out exactly as the reference
@@ -102,6 +106,7 @@ typedef struct sage_attn_args {
   int is_causal;
   int out_dtype;   /* SAGE_DTYPE_* */
   float sm_scale;
+  void* debug_s;   /* NULL, or int32 [B,Hq,ceil256(Nq),128]: raw QK^T of kv tile 0 (test hook) */
 } sage_attn_args;
 
 int sage_attn_i8_f16(const sage_attn_args* a, void* stream);

@@ -1,0 +1,83 @@
+"""ctypes binding of libsage_b200.so (include/sage_b200.h).
+
+There is no CPU fallback: if the library is missing it is built (nvcc), and if that fails the
+import raises.  Every call checks the int status and raises ValueError (bad argument) or
+RuntimeError (CUDA error) with the library's message, mirroring the reference's pybind
+exception mapping (std::invalid_argument -> ValueError, TORCH_CHECK -> RuntimeError;
+/root/reference/csrc/dispatch_utils.h:31-35, /root/reference/csrc/utils.cuh:20-37).
+"""
+import ctypes
+import os
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_PKG, "libsage_b200.so")
+
+c_i64 = ctypes.c_int64
+c_int = ctypes.c_int
+c_f32 = ctypes.c_float
+c_vp = ctypes.c_void_p
+
+
+class Tensor4(ctypes.Structure):
+    _fields_ = [("ptr", c_vp), ("stride_b", c_i64), ("stride_h", c_i64), ("stride_n", c_i64)]
+
+
+class AttnArgs(ctypes.Structure):
+    _fields_ = [
+        ("q8", Tensor4), ("k8", Tensor4), ("v", Tensor4), ("o", Tensor4),
+        ("q_scale", c_vp), ("k_scale", c_vp), ("v_scale", c_vp), ("v_mean", c_vp), ("lse", c_vp),
+        ("B", c_int), ("Hq", c_int), ("Hkv", c_int), ("Nq", c_int), ("Nk", c_int), ("D", c_int),
+        ("npad_v", c_int), ("gran", c_int), ("warp_q", c_int), ("is_causal", c_int),
+        ("out_dtype", c_int), ("sm_scale", c_f32), ("debug_s", c_vp),
+    ]
+
+
+# name -> (restype, argtypes); the single source of truth for the exported surface
+SIGNATURES = {
+    "sage_last_error": (ctypes.c_char_p, []),
+    "sage_version": (c_int, []),
+    "sage_seq_mean_workspace_bytes": (ctypes.c_size_t, [c_int] * 4),
+    "sage_seq_mean": (c_int, [Tensor4, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp]),
+    "sage_quant_int8": (c_int, [Tensor4, c_vp, Tensor4, c_vp, c_int, c_int, c_int, c_int, c_int, c_int,
+                                c_int, c_int, c_f32, c_vp]),
+    "sage_quant_per_thread_int8": (c_int, [Tensor4, c_vp, Tensor4, c_vp, c_int, c_int, c_int, c_int, c_int,
+                                           c_int, c_int, c_vp]),
+    "sage_sub_mean": (c_int, [Tensor4, c_vp, Tensor4, c_int, c_int, c_int, c_int, c_int, c_vp]),
+    "sage_per_channel_fp8_workspace_bytes": (ctypes.c_size_t, [c_int] * 4),
+    "sage_per_channel_fp8": (c_int, [Tensor4, c_vp, c_i64, c_i64, c_i64, c_vp, c_vp, c_int, c_int, c_int,
+                                     c_int, c_int, c_int, c_f32, c_int, c_vp, c_vp]),
+    "sage_attn_i8_f16": (c_int, [ctypes.POINTER(AttnArgs), c_vp]),
+    "sage_attn_i8_f8": (c_int, [ctypes.POINTER(AttnArgs), c_vp]),
+}
+
+_lib = None
+
+
+def load():
+    """Load (building first if needed) and return the ctypes library handle."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(_LIB_PATH):
+        from . import build as _build
+        _build.build()
+    lib = ctypes.CDLL(_LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is missing: fail loudly
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc):
+    if rc == 0:
+        return
+    msg = load().sage_last_error().decode("utf-8", "replace")
+    if rc < 0:
+        raise ValueError(msg)
+    raise RuntimeError(f"CUDA error {rc}: {msg}")
+
+
+DTYPE_F16, DTYPE_BF16 = 0, 1
+GRAN_PER_BLOCK, GRAN_PER_WARP, GRAN_PER_THREAD = 1, 2, 3

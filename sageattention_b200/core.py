@@ -1,0 +1,233 @@
+"""Public attention API - a drop-in for /root/reference/sageattention/core.py on B200.
+
+    sageattn(q, k, v, tensor_layout="HND", is_causal=False, sm_scale=None, smooth_k=True, return_lse=False)
+    sageattn_qk_int8_pv_fp16_cuda(...)      reference: core.py:480-653
+    sageattn_qk_int8_pv_fp8_cuda(...)       reference: core.py:656-905 (upstream semantics)
+
+Host code is Python/PyTorch (allocation, streams); all arithmetic runs in libsage_b200.so
+(hand-written sm_100a CUDA, include/sage_b200.h).  There is no Triton path, no multi-arch dispatch
+and no CPU fallback: a CPU tensor or a missing library raises.
+"""
+import warnings
+from typing import Any, Optional
+
+import torch
+
+from . import _lib
+from .quant import (_dims, _dtype_code, _require_cuda, _stream, per_channel_fp8, per_thread_int8,
+                    per_warp_int8, seq_mean, sub_mean)
+
+_LOG2E = 1.44269504
+
+
+def _pad_head_dim(q, k, v):
+    """Zero-pad head_dim to 64 / 128 like core.py:590-601."""
+    d = q.size(-1)
+    if d < 64:
+        pad = 64 - d
+    elif 64 < d < 128:
+        pad = 128 - d
+    elif d > 128:
+        raise ValueError(f"Unsupported head_dim: {d}")
+    else:
+        return q, k, v
+    f = torch.nn.functional.pad
+    return f(q, (0, pad)), f(k, (0, pad)), f(v, (0, pad))
+
+
+def _check_inputs(q, k, v, qk_quant_gran):
+    assert q.is_cuda, "Input tensors must be on cuda."
+    assert q.dtype in [torch.float16, torch.bfloat16], \
+        "Input tensors must be in dtype of torch.float16 or torch.bfloat16"
+    assert qk_quant_gran in ["per_warp", "per_thread"], "qk_quant_gran must be either 'per_warp' or 'per_thread'."
+    assert q.device == k.device == v.device, "All tensors must be on the same device."
+    assert q.dtype == k.dtype == v.dtype, "All tensors must have the same dtype."
+
+
+def _smooth_k(q, k, tensor_layout, return_lse):
+    """km = mean over the sequence (input dtype) and the LSE correction q.km (core.py:611-617).
+    With GQA the reference's matmul only broadcasts when Hq == Hkv; here km is expanded per q head."""
+    b, hk, nk, d, _ = _dims(k, tensor_layout)
+    km = seq_mean(k, tensor_layout)  # [B, Hkv, D]
+    lse_correction = None
+    if return_lse:
+        hq = q.size(1) if tensor_layout == "HND" else q.size(2)
+        kmq = km if hq == hk else km.repeat_interleave(hq // hk, dim=1)
+        qh = q if tensor_layout == "HND" else q.transpose(1, 2)
+        lse_correction = torch.matmul(qh, kmq.unsqueeze(-1)).squeeze(-1).to(torch.float32)
+    return km, lse_correction
+
+
+def _quantize_qk(q, k, km, qk_quant_gran, tensor_layout, warp_q):
+    if qk_quant_gran == "per_warp":
+        return per_warp_int8(q, k, km, tensor_layout=tensor_layout, BLKQ=128, WARPQ=warp_q, BLKK=64)
+    return per_thread_int8(q, k, km, tensor_layout=tensor_layout, BLKQ=128, WARPQ=warp_q, BLKK=64, WARPK=64)
+
+
+def _launch(fp8, q_int8, k_int8, v, o, q_scale, k_scale, v_scale, v_mean, tensor_layout, is_causal, gran,
+            warp_q, sm_scale, return_lse, npad_v=0, debug_s=None):
+    """One call into sage_attn_i8_f8 / sage_attn_i8_f16; returns the base-2 LSE or None."""
+    lib = _lib.load()
+    b, hq, nq, d, q4 = _dims(q_int8, tensor_layout)
+    _, hk, nk, _, k4 = _dims(k_int8, tensor_layout)
+    _, _, _, _, o4 = _dims(o, tensor_layout)
+    if fp8:
+        # v_fp8 is [B,H,D,Npad] (HND) or [B,D,H,Npad] (NHD); rows of Npad bytes
+        if tensor_layout == "HND":
+            v4 = _lib.Tensor4(v.data_ptr(), v.stride(0), v.stride(1), v.stride(2))
+        else:
+            v4 = _lib.Tensor4(v.data_ptr(), v.stride(0), v.stride(2), v.stride(1))
+        npad_v = v.size(-1)
+    else:
+        _, _, _, _, v4 = _dims(v, tensor_layout)
+    lse = torch.empty((b, hq, nq), dtype=torch.float32, device=o.device) if return_lse else None
+    a = _lib.AttnArgs()
+    a.q8, a.k8, a.v, a.o = q4, k4, v4, o4
+    a.q_scale, a.k_scale = q_scale.data_ptr(), k_scale.data_ptr()
+    a.v_scale = v_scale.data_ptr() if v_scale is not None else None
+    a.v_mean = v_mean.data_ptr() if v_mean is not None else None
+    a.lse = lse.data_ptr() if lse is not None else None
+    a.B, a.Hq, a.Hkv, a.Nq, a.Nk, a.D = b, hq, hk, nq, nk, d
+    a.npad_v = npad_v
+    a.gran = gran
+    a.warp_q = warp_q
+    a.is_causal = 1 if is_causal else 0
+    a.out_dtype = _dtype_code(o)
+    a.sm_scale = float(sm_scale)
+    a.debug_s = debug_s.data_ptr() if debug_s is not None else None
+    fn = lib.sage_attn_i8_f8 if fp8 else lib.sage_attn_i8_f16
+    with torch.cuda.device(o.device):
+        _lib.check(fn(a, _stream(o)))
+    return lse
+
+
+def _finish(o, lse, lse_correction, sm_scale, head_dim_og, return_lse):
+    o = o[..., :head_dim_og]
+    if not return_lse:
+        return o
+    lse = lse / _LOG2E
+    if lse_correction is not None:
+        lse = lse + lse_correction * sm_scale
+    return o, lse
+
+
+@torch.compiler.disable
+def sageattn_qk_int8_pv_fp16_cuda(
+    q: torch.Tensor,
+    k: torch.Tensor,
+    v: torch.Tensor,
+    tensor_layout: str = "HND",
+    is_causal: bool = False,
+    qk_quant_gran: str = "per_thread",
+    sm_scale: Optional[float] = None,
+    pv_accum_dtype: str = "fp32",
+    smooth_k: bool = True,
+    smooth_v: bool = False,
+    return_lse: bool = False,
+    **kwargs: Any,
+) -> torch.Tensor:
+    """INT8 QK^T + FP16 P.V (reference core.py:480-653).
+
+    pv_accum_dtype in {"fp32", "fp16", "fp16+fp32"} is accepted for compatibility; on sm_100a the
+    P.V accumulator always lives in TMEM as fp32 (the reference's fp16 accumulators exist only
+    because mma.sync fp16 accumulation was faster on sm80), so all three give fp32-accumulated
+    results.  `smooth_v` is honoured for "fp16" as in the reference and ignored (with the same
+    warning) otherwise.  Extra kwargs (attn_mask, dropout_p, ...) are ignored like the reference.
+    """
+    _check_inputs(q, k, v, qk_quant_gran)
+    if pv_accum_dtype not in ("fp32", "fp16", "fp16+fp32"):
+        raise ValueError(f"Unsupported pv_accum_dtype: {pv_accum_dtype}")
+    dtype = q.dtype
+    head_dim_og = q.size(-1)
+    q, k, v = _pad_head_dim(q, k, v)
+    assert q.stride(-1) == 1 and k.stride(-1) == 1 and v.stride(-1) == 1, "Last dim of qkv must be contiguous."
+    if sm_scale is None:
+        sm_scale = head_dim_og ** -0.5
+    km, lse_correction = _smooth_k(q, k, tensor_layout, return_lse) if smooth_k else (None, None)
+    warp_q = 16 if (q.size(-1) == 128 and pv_accum_dtype == "fp16+fp32") else 32
+    q_int8, q_scale, k_int8, k_scale = _quantize_qk(q, k, km, qk_quant_gran, tensor_layout, warp_q)
+    o = torch.empty(q.size(), dtype=dtype, device=q.device)
+    if pv_accum_dtype in ["fp32", "fp16+fp32"] and smooth_v:
+        warnings.warn(f"pv_accum_dtype is {pv_accum_dtype}, smooth_v will be ignored.")
+        smooth_v = False
+    v_mean = None
+    if smooth_v:
+        v16, vm = sub_mean(v, tensor_layout=tensor_layout)
+        v_mean = vm.to(torch.float32)
+    else:
+        v16 = v.to(torch.float16)
+    gran = _lib.GRAN_PER_THREAD if qk_quant_gran == "per_thread" else _lib.GRAN_PER_WARP
+    lse = _launch(False, q_int8, k_int8, v16, o, q_scale, k_scale, None, v_mean, tensor_layout, is_causal, gran,
+                  warp_q, sm_scale, return_lse)
+    return _finish(o, lse, lse_correction, sm_scale, head_dim_og, return_lse)
+
+
+@torch.compiler.disable
+def sageattn_qk_int8_pv_fp8_cuda(
+    q: torch.Tensor,
+    k: torch.Tensor,
+    v: torch.Tensor,
+    tensor_layout: str = "HND",
+    is_causal: bool = False,
+    qk_quant_gran: str = "per_thread",
+    sm_scale: Optional[float] = None,
+    pv_accum_dtype: str = "fp32+fp16",
+    smooth_k: bool = True,
+    smooth_v: bool = False,
+    return_lse: bool = False,
+    **kwargs: Any,
+) -> torch.Tensor:
+    """INT8 QK^T + FP8(e4m3) P.V (reference core.py:656-905, upstream semantics).
+
+    pv_accum_dtype in {"fp32", "fp32+fp32", "fp32+fp16"}: accumulation is always fp32 in TMEM;
+    the string still selects the V quantisation range exactly as the reference does
+    (scale_max 448, or 2.25 for "fp32+fp16", core.py:818-820) and whether smooth_v applies.
+    """
+    _check_inputs(q, k, v, qk_quant_gran)
+    if pv_accum_dtype not in ("fp32", "fp32+fp32", "fp32+fp16"):
+        raise ValueError(f"Unsupported pv_accum_dtype: {pv_accum_dtype}")
+    dtype = q.dtype
+    head_dim_og = q.size(-1)
+    q, k, v = _pad_head_dim(q, k, v)
+    assert q.stride(-1) == 1 and k.stride(-1) == 1 and v.stride(-1) == 1, "Last dim of qkv must be contiguous."
+    if sm_scale is None:
+        sm_scale = head_dim_og ** -0.5
+    km, lse_correction = _smooth_k(q, k, tensor_layout, return_lse) if smooth_k else (None, None)
+    q_int8, q_scale, k_int8, k_scale = _quantize_qk(q, k, km, qk_quant_gran, tensor_layout, 32)
+    o = torch.empty(q.size(), dtype=dtype, device=q.device)
+    if pv_accum_dtype == "fp32+fp32" and smooth_v:
+        warnings.warn("pv_accum_dtype is 'fp32+fp32', smooth_v will be ignored.")
+        smooth_v = False
+    if pv_accum_dtype == "fp32+fp16" and smooth_v:
+        warnings.warn("pv_accum_dtype is 'fp32+fp16', smooth_v will be ignored.")
+        smooth_v = False
+    quant_v_scale_max = 2.25 if pv_accum_dtype == "fp32+fp16" else 448.0
+    kv_len = k.size(2) if tensor_layout == "HND" else k.size(1)
+    # the reference zero-pads V to a multiple of 128 tokens first (core.py:822-828); the kernel
+    # reproduces that padding's effect on Npad / the smooth_v mean without the extra copy
+    v_fp8, v_scale, vm = per_channel_fp8(v, tensor_layout=tensor_layout, scale_max=quant_v_scale_max,
+                                         smooth_v=smooth_v, _n_stat=(kv_len + 127) // 128 * 128)
+    gran = _lib.GRAN_PER_THREAD if qk_quant_gran == "per_thread" else _lib.GRAN_PER_WARP
+    lse = _launch(True, q_int8, k_int8, v_fp8, o, q_scale, k_scale, v_scale, vm, tensor_layout, is_causal, gran,
+                  32, sm_scale, return_lse)
+    return _finish(o, lse, lse_correction, sm_scale, head_dim_og, return_lse)
+
+
+def sageattn(
+    q: torch.Tensor,
+    k: torch.Tensor,
+    v: torch.Tensor,
+    tensor_layout: str = "HND",
+    is_causal: bool = False,
+    sm_scale: Optional[float] = None,
+    smooth_k: bool = True,
+    return_lse: bool = False,
+    **kwargs: Any,
+):
+    """Reference: core.py:80-158.  The reference picks a kernel per GPU architecture (and the fork
+    hard-wires the fp8 path, core.py:144); this package targets sm_100a only, so `sageattn` is the
+    INT8-QK / FP8-PV tcgen05 kernel with fp32 accumulation.  `smooth_k` is accepted and forwarded
+    (the reference drops it inside **kwargs)."""
+    return sageattn_qk_int8_pv_fp8_cuda(q, k, v, tensor_layout=tensor_layout, is_causal=is_causal,
+                                        sm_scale=sm_scale, pv_accum_dtype="fp32+fp32", smooth_k=smooth_k,
+                                        return_lse=return_lse)

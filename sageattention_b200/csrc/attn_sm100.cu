@@ -57,6 +57,7 @@ struct AttnKernelParams {
   const float* v_mean;   // may be null
   void* o;
   float* lse;  // may be null
+  int* debug_s;  // may be null: raw S of kv tile 0, [B,Hq,ceil256(Nq),128] s32
   int B, Hq, Hkv, Nq, Nk, Npad_v;
   long long o_stride_b, o_stride_h, o_stride_n;  // elements
   int q_scale_per_bh, k_scale_per_bh;            // entries per (b,h)
@@ -220,6 +221,12 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
       tmem_ld32(tS + 64, s2);
       tmem_ld32(tS + 96, s3);
       tc_wait_ld();
+    }
+    if (p.debug_s != nullptr && j == 0) {
+      const int nq_pad = (p.Nq + 255) / 256 * 256;
+      int* dst = p.debug_s + ((size_t)(b * p.Hq + h) * nq_pad + q_row) * 128;
+#pragma unroll
+      for (int c = 0; c < 128; ++c) dst[c] = (int)s[c];
     }
     const int kv0 = j * kTileKV;
     int lim = p.Nk - 1 - kv0;
@@ -556,6 +563,7 @@ static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
   p.v_mean = a->v_mean;
   p.o = a->o.ptr;
   p.lse = a->lse;
+  p.debug_s = reinterpret_cast<int*>(a->debug_s);
   p.B = a->B; p.Hq = a->Hq; p.Hkv = a->Hkv; p.Nq = a->Nq; p.Nk = a->Nk; p.Npad_v = a->npad_v;
   p.o_stride_b = a->o.stride_b; p.o_stride_h = a->o.stride_h; p.o_stride_n = a->o.stride_n;
   p.gran = a->gran;

@@ -52,7 +52,7 @@ __device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
 }
 // Bounded spin: a lost arrival traps (reported as a launch failure) instead of hanging the GPU.
 #ifndef SAGE_MBAR_SPIN_LIMIT
-#define SAGE_MBAR_SPIN_LIMIT (1u << 28)
+#define SAGE_MBAR_SPIN_LIMIT (1u << 24)
 #endif
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   uint32_t spins = 0;

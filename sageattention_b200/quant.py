@@ -1,0 +1,188 @@
+"""Quantizers with the reference's signatures, backed by the sm_100a C-ABI library.
+
+Mirrors /root/reference/sageattention/quant.py (per_block_int8 :23, per_warp_int8 :106,
+sub_mean :183, per_channel_fp8 :225) and the Triton default-granularity quantizer
+/root/reference/sageattention/triton/quant_per_thread.py:158 (per_thread_int8), which the
+reference's CUDA entry points use by default and which exists here as a CUDA kernel because this
+package has no Triton path.
+
+Outputs are bit-exact with the reference quantizers on identical inputs (tests/test_quant_gpu.py
+checks this against the reference's own compiled sources).  No CPU fallback exists.
+"""
+from typing import Optional
+
+import torch
+
+from . import _lib
+
+
+def _dtype_code(t: torch.Tensor) -> int:
+    if t.dtype == torch.float16:
+        return _lib.DTYPE_F16
+    if t.dtype == torch.bfloat16:
+        return _lib.DTYPE_BF16
+    raise ValueError(f"Unsupported dtype {t.dtype}: tensors must be torch.float16 or torch.bfloat16")
+
+
+def _dims(t: torch.Tensor, tensor_layout: str):
+    """-> (B, H, N, D, Tensor4) for a [B,H,N,D] ("HND") or [B,N,H,D] ("NHD") tensor."""
+    if t.dim() != 4:
+        raise RuntimeError("Tensor must have 4 dimensions")
+    if t.stride(-1) != 1:
+        raise RuntimeError("Tensor must be contiguous at last dimension")
+    if tensor_layout == "HND":
+        b, h, n, d = t.shape
+        t4 = _lib.Tensor4(t.data_ptr(), t.stride(0), t.stride(1), t.stride(2))
+    elif tensor_layout == "NHD":
+        b, n, h, d = t.shape
+        t4 = _lib.Tensor4(t.data_ptr(), t.stride(0), t.stride(2), t.stride(1))
+    else:
+        raise ValueError(f"Unknown tensor layout: {tensor_layout}")
+    return b, h, n, d, t4
+
+
+def _stream(t: torch.Tensor):
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _require_cuda(*ts):
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("Tensor must be on CUDA (sageattention_b200 has no CPU path)")
+
+
+def _mean_ptr(km: Optional[torch.Tensor], b, h, d, like: torch.Tensor):
+    if km is None:
+        return None, None
+    km = km.reshape(b, h, d)
+    if km.dtype != like.dtype:
+        raise RuntimeError("km must have the same dtype as the tensor it smooths")
+    km = km.contiguous()
+    return km, km.data_ptr()
+
+
+def seq_mean(x: torch.Tensor, tensor_layout: str = "HND") -> torch.Tensor:
+    """`x.mean(dim=seq)` in one deterministic kernel -> [B, H, D], same dtype as x
+    (replaces the torch reduction at /root/reference/sageattention/core.py:612)."""
+    _require_cuda(x)
+    lib = _lib.load()
+    b, h, n, d, x4 = _dims(x, tensor_layout)
+    out = torch.empty((b, h, d), dtype=x.dtype, device=x.device)
+    ws = torch.empty(lib.sage_seq_mean_workspace_bytes(b, h, n, d), dtype=torch.uint8, device=x.device)
+    with torch.cuda.device(x.device):
+        _lib.check(lib.sage_seq_mean(x4, out.data_ptr(), b, h, n, d, _dtype_code(x), ws.data_ptr(), _stream(x)))
+    return out
+
+
+def _quant_block(x, km, block, sm_scale, tensor_layout, scale_per_bh=None):
+    lib = _lib.load()
+    b, h, n, d, x4 = _dims(x, tensor_layout)
+    out = torch.empty(x.shape, dtype=torch.int8, device=x.device)
+    _, _, _, _, o4 = _dims(out, tensor_layout)
+    nblk = (n + block - 1) // block
+    if scale_per_bh is None:
+        scale_per_bh = nblk
+    # entries past ceil(N/block) are never written by the reference either (torch.empty there);
+    # zeros keep them harmless
+    scale = (torch.empty if scale_per_bh == nblk else torch.zeros)(
+        (b, h, scale_per_bh), dtype=torch.float32, device=x.device)
+    km_c, km_ptr = _mean_ptr(km, b, h, d, x)
+    with torch.cuda.device(x.device):
+        _lib.check(lib.sage_quant_int8(x4, km_ptr, o4, scale.data_ptr(), b, h, n, d, _dtype_code(x), block,
+                                       scale_per_bh, 0 if sm_scale is None else 1,
+                                       0.0 if sm_scale is None else float(sm_scale), _stream(x)))
+    return out, scale
+
+
+def per_block_int8(q, k, km=None, BLKQ=128, BLKK=64, sm_scale=None, tensor_layout="HND"):
+    """Reference: /root/reference/sageattention/quant.py:23-104.  Q is pre-multiplied by
+    sm_scale * 1.44269504 before quantisation; K is optionally smoothed by km."""
+    _require_cuda(q, k, km)
+    head_dim = q.size(-1)
+    if sm_scale is None:
+        sm_scale = head_dim ** -0.5
+    sm_scale = sm_scale * 1.44269504
+    q_int8, q_scale = _quant_block(q, None, BLKQ, sm_scale, tensor_layout)
+    k_int8, k_scale = _quant_block(k, km, BLKK, None, tensor_layout)
+    return q_int8, q_scale, k_int8, k_scale
+
+
+def per_warp_int8(q, k, km=None, BLKQ=128, WARPQ=32, BLKK=64, tensor_layout="HND"):
+    """Reference: /root/reference/sageattention/quant.py:106-181.  q_scale has
+    ceil(Nq/BLKQ)*(BLKQ/WARPQ) entries per head (only the first ceil(Nq/WARPQ) are written,
+    as in the reference, whose scale buffer is torch.empty)."""
+    _require_cuda(q, k, km)
+    n = q.size(2) if tensor_layout == "HND" else q.size(1)
+    q_int8, q_scale = _quant_block(q, None, WARPQ, None, tensor_layout,
+                                   scale_per_bh=((n + BLKQ - 1) // BLKQ) * (BLKQ // WARPQ))
+    k_int8, k_scale = _quant_block(k, km, BLKK, None, tensor_layout)
+    return q_int8, q_scale, k_int8, k_scale
+
+
+def per_thread_int8(q, k, km=None, BLKQ=128, WARPQ=32, BLKK=64, WARPK=64, sm_scale=None, tensor_layout="HND"):
+    """Reference: /root/reference/sageattention/triton/quant_per_thread.py:158-208 (Triton).
+    Same group structure and arithmetic, as a CUDA kernel."""
+    _require_cuda(q, k, km)
+    if WARPK != 64 or BLKK != 64 or BLKQ != 128:
+        raise ValueError("per_thread_int8 supports BLKQ=128, BLKK=64, WARPK=64 (the reference's only use)")
+    lib = _lib.load()
+    b, hq, nq, d, q4 = _dims(q, tensor_layout)
+    _, hk, nk, _, k4 = _dims(k, tensor_layout)
+    q_int8 = torch.empty(q.shape, dtype=torch.int8, device=q.device)
+    k_int8 = torch.empty(k.shape, dtype=torch.int8, device=k.device)
+    _, _, _, _, qo4 = _dims(q_int8, tensor_layout)
+    _, _, _, _, ko4 = _dims(k_int8, tensor_layout)
+    q_scale = torch.empty((b, hq, (nq + BLKQ - 1) // BLKQ * (BLKQ // WARPQ) * 8), dtype=torch.float32, device=q.device)
+    k_scale = torch.empty((b, hk, (nk + BLKK - 1) // BLKK * (BLKK // WARPK) * 4), dtype=torch.float32, device=q.device)
+    km_c, km_ptr = _mean_ptr(km, b, hk, d, k)
+    with torch.cuda.device(q.device):
+        _lib.check(lib.sage_quant_per_thread_int8(q4, None, qo4, q_scale.data_ptr(), b, hq, nq, d, _dtype_code(q),
+                                                  0, WARPQ, _stream(q)))
+        _lib.check(lib.sage_quant_per_thread_int8(k4, km_ptr, ko4, k_scale.data_ptr(), b, hk, nk, d, _dtype_code(k),
+                                                  1, 64, _stream(k)))
+    return q_int8, q_scale, k_int8, k_scale
+
+
+def sub_mean(v, tensor_layout="HND", vm=None):
+    """Reference: /root/reference/sageattention/quant.py:183-223 -> (v_smoothed fp16, vm input dtype).
+    `vm` (optional, [B,H,D] in v's dtype) overrides the internally computed mean."""
+    _require_cuda(v)
+    lib = _lib.load()
+    b, h, n, d, v4 = _dims(v, tensor_layout)
+    if vm is None:
+        vm = seq_mean(v, tensor_layout)
+    vm = vm.reshape(b, h, d).contiguous()
+    out = torch.empty(v.shape, dtype=torch.float16, device=v.device)
+    _, _, _, _, o4 = _dims(out, tensor_layout)
+    with torch.cuda.device(v.device):
+        _lib.check(lib.sage_sub_mean(v4, vm.data_ptr(), o4, b, h, n, d, _dtype_code(v), _stream(v)))
+    return out, vm
+
+
+def per_channel_fp8(v, tensor_layout="HND", scale_max=448.0, smooth_v=True, _n_stat=None):
+    """Reference: /root/reference/sageattention/quant.py:225-322 with upstream NVIDIA semantics
+    (float8_e4m3fn; the fork's e4m3fnuz at quant.py:312 is an AMD format).
+    -> (v_fp8 [B,H,D,Npad] ("HND") or [B,D,H,Npad] ("NHD"), v_scale [B,H,D] f32, vm [B,H,D] f32 | None)
+
+    `_n_stat` (internal): behave as if v had been zero-padded along the sequence to that many
+    tokens first, as core.py:822-828 does, without materialising the padded copy."""
+    _require_cuda(v)
+    lib = _lib.load()
+    b, h, n, d, v4 = _dims(v, tensor_layout)
+    n_stat = n if _n_stat is None else max(n, int(_n_stat))
+    npad = (n_stat + 63) // 64 * 64
+    if tensor_layout == "HND":
+        v_fp8 = torch.empty((b, h, d, npad), dtype=torch.float8_e4m3fn, device=v.device)
+        sb, sh, sd = v_fp8.stride(0), v_fp8.stride(1), v_fp8.stride(2)
+    else:
+        v_fp8 = torch.empty((b, d, h, npad), dtype=torch.float8_e4m3fn, device=v.device)
+        sb, sh, sd = v_fp8.stride(0), v_fp8.stride(2), v_fp8.stride(1)
+    v_scale = torch.empty((b, h, d), dtype=torch.float32, device=v.device)
+    vm = torch.empty((b, h, d), dtype=torch.float32, device=v.device) if smooth_v else None
+    ws = torch.empty(lib.sage_per_channel_fp8_workspace_bytes(b, h, n, d), dtype=torch.uint8, device=v.device)
+    with torch.cuda.device(v.device):
+        _lib.check(lib.sage_per_channel_fp8(v4, v_fp8.data_ptr(), sb, sh, sd, v_scale.data_ptr(),
+                                            vm.data_ptr() if smooth_v else None, b, h, n, n_stat, d,
+                                            _dtype_code(v), float(scale_max), 1 if smooth_v else 0,
+                                            ws.data_ptr(), _stream(v)))
+    return v_fp8, v_scale, vm

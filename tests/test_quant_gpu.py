@@ -1,0 +1,155 @@
+"""GPU parity of the pre-pass quantizers (through the C ABI) against
+  (a) the reference's own CUDA quantizers compiled from /root/reference (oracle/_ref/_ref_fused.so):
+      BIT-EXACT codes and scales - the north-star's first correctness gate;
+  (b) the CPU oracle (oracle/sage_oracle.py) on the same seeded inputs.
+"""
+import pytest
+import torch
+
+import sageattention_b200 as sb
+from oracle import sage_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+DEV = "cuda:0"
+
+
+def make(b, h, n, d, dtype, layout, seed=0, bias=2.0):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    x = torch.randn(b, h, n, d, generator=g) + bias * torch.randn(1, h, 1, d, generator=g)
+    x = x.to(dtype).to(DEV)
+    if layout == "NHD":
+        x = x.transpose(1, 2).contiguous()
+    return x
+
+
+def ref_per_warp(ref_fused, q, k, km, BLKQ, WARPQ, BLKK, layout):
+    """The reference's per_warp_int8 (quant.py:106-181) re-stated over the reference's compiled launchers."""
+    tl_ = 0 if layout == "NHD" else 1
+    if layout == "HND":
+        b, hq, nq, d = q.shape
+        _, hk, nk, _ = k.shape
+    else:
+        b, nq, hq, d = q.shape
+        _, nk, hk, _ = k.shape
+    q8 = torch.empty(q.shape, dtype=torch.int8, device=q.device)
+    k8 = torch.empty(k.shape, dtype=torch.int8, device=k.device)
+    qs = torch.zeros((b, hq, ((nq + BLKQ - 1) // BLKQ) * (BLKQ // WARPQ)), device=q.device, dtype=torch.float32)
+    ks = torch.zeros((b, hk, (nk + BLKK - 1) // BLKK), device=q.device, dtype=torch.float32)
+    ref_fused.quant_per_warp_int8_cuda(q, q8, qs, BLKQ, WARPQ, tl_)
+    if km is not None:
+        ref_fused.quant_per_block_int8_fuse_sub_mean_cuda(k, km, k8, ks, BLKK, tl_)
+    else:
+        ref_fused.quant_per_block_int8_cuda(k, k8, ks, BLKK, tl_)
+    return q8, qs, k8, ks
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("layout", ["HND", "NHD"])
+@pytest.mark.parametrize("n,d", [(256, 128), (1000, 128), (333, 64), (64, 64), (17, 128)])
+@pytest.mark.parametrize("warpq", [32, 16])
+def test_per_warp_bit_exact_vs_reference(ref_fused, dtype, layout, n, d, warpq):
+    q = make(2, 3, n, d, dtype, layout, 1)
+    k = make(2, 3, n + 37, d, dtype, layout, 2)
+    km = k.mean(dim=2 if layout == "HND" else 1)
+    for use_km in (km, None):
+        mine = sb.per_warp_int8(q, k, use_km, WARPQ=warpq, tensor_layout=layout)
+        ref = ref_per_warp(ref_fused, q, k, use_km, 128, warpq, 64, layout)
+        nw = (n + warpq - 1) // warpq
+        assert torch.equal(mine[0], ref[0]), "q codes differ"
+        assert torch.equal(mine[1][..., :nw], ref[1][..., :nw]), "q scales differ"
+        assert torch.equal(mine[2], ref[2]), "k codes differ"
+        assert torch.equal(mine[3], ref[3]), "k scales differ"
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("n,d", [(512, 128), (777, 64)])
+def test_per_block_bit_exact_vs_reference(ref_fused, dtype, n, d):
+    q = make(1, 4, n, d, dtype, "HND", 3)
+    k = make(1, 4, n, d, dtype, "HND", 4)
+    km = k.mean(dim=2)
+    mine = sb.per_block_int8(q, k, km, sm_scale=0.11)
+    q8 = torch.empty_like(q, dtype=torch.int8)
+    k8 = torch.empty_like(k, dtype=torch.int8)
+    qs = torch.empty((1, 4, (n + 127) // 128), device=DEV, dtype=torch.float32)
+    ks = torch.empty((1, 4, (n + 63) // 64), device=DEV, dtype=torch.float32)
+    ref_fused.quant_per_block_int8_sm_scale_cuda(q, q8, qs, 0.11 * 1.44269504, 128, 1)
+    ref_fused.quant_per_block_int8_fuse_sub_mean_cuda(k, km, k8, ks, 64, 1)
+    assert torch.equal(mine[0], q8) and torch.equal(mine[1], qs)
+    assert torch.equal(mine[2], k8) and torch.equal(mine[3], ks)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("layout", ["HND", "NHD"])
+@pytest.mark.parametrize("n,d", [(256, 128), (1000, 128), (130, 64), (50, 64)])
+@pytest.mark.parametrize("smooth,scale_max", [(False, 448.0), (True, 448.0), (False, 2.25)])
+def test_per_channel_fp8_bit_exact_vs_reference(ref_fused, dtype, layout, n, d, smooth, scale_max):
+    v = make(2, 2, n, d, dtype, layout, 5, bias=1.0)
+    v8, vs, vm = sb.per_channel_fp8(v, tensor_layout=layout, scale_max=scale_max, smooth_v=smooth)
+    # reference pipeline (quant.py:270-322) over the reference's compiled launchers
+    tl_ = 0 if layout == "NHD" else 1
+    npad = (n + 63) // 64 * 64
+    shape = (2, 2, d, npad) if layout == "HND" else (2, d, 2, npad)
+    vt = torch.zeros(shape, dtype=dtype, device=DEV)
+    ref_fused.transpose_pad_permute_cuda(v, vt, tl_)
+    r8 = torch.zeros(shape, dtype=torch.float8_e4m3fn, device=DEV)
+    rs = torch.zeros((2, 2, d), dtype=torch.float32, device=DEV)
+    rm = torch.empty((2, 2, d), dtype=torch.float32, device=DEV)
+    if smooth:
+        ref_fused.mean_scale_fuse_quant_cuda(vt, r8, rm, rs, n, scale_max, tl_)
+    else:
+        ref_fused.scale_fuse_quant_cuda(vt, r8, rs, n, scale_max, tl_)
+    assert v8.shape == r8.shape
+    assert torch.equal(vs, rs), "v_scale differs"
+    if smooth:
+        assert torch.equal(vm, rm), "v_mean differs"
+    assert torch.equal(v8.view(torch.uint8), r8.view(torch.uint8)), "fp8 codes differ"
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("layout", ["HND", "NHD"])
+def test_sub_mean_bit_exact_vs_reference(ref_fused, dtype, layout):
+    v = make(2, 3, 300, 128, dtype, layout, 6)
+    vm = v.mean(dim=2 if layout == "HND" else 1)
+    mine, _ = sb.sub_mean(v, tensor_layout=layout, vm=vm)
+    ref = torch.empty(v.shape, dtype=torch.float16, device=DEV)
+    ref_fused.sub_mean_cuda(v, vm, ref, 0 if layout == "NHD" else 1)
+    assert torch.equal(mine, ref)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("n,d", [(4096, 128), (1000, 64), (100, 128)])
+def test_seq_mean_matches_torch(dtype, n, d):
+    k = make(2, 4, n, d, dtype, "HND", 7)
+    mine = sb.seq_mean(k)
+    ref = k.mean(dim=2)
+    # both reduce in fp32 and round once to the input dtype; the summation order differs, so a
+    # value on a rounding boundary may land on the neighbouring code: <= 1 ulp, and rare
+    diff = (mine.float() - ref.float()).abs()
+    ulp = ref.float().abs() * (2.0 ** -10 if dtype == torch.float16 else 2.0 ** -7) + 1e-7
+    assert (diff <= ulp).all()
+    assert (mine != ref).float().mean().item() < 0.01
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("layout", ["HND", "NHD"])
+@pytest.mark.parametrize("n,d,warpq", [(256, 128, 32), (1000, 128, 16), (333, 64, 32), (40, 64, 32)])
+def test_quantizers_match_cpu_oracle(dtype, layout, n, d, warpq):
+    """CUDA path vs CPU oracle.  The oracle divides in IEEE arithmetic, the CUDA reference (and
+    therefore our kernels) with div.approx: scales may differ by 1 ulp and a code by +-1 when
+    x*inv lands within an ulp of a rounding boundary.  Bound: <= 0.1% of codes, each by at most 1."""
+    q = make(1, 2, n, d, dtype, layout, 8)
+    k = make(1, 2, n + 5, d, dtype, layout, 9)
+    km = k.mean(dim=2 if layout == "HND" else 1)
+    for name in ("per_warp_int8", "per_thread_int8"):
+        mine = getattr(sb, name)(q, k, km, WARPQ=warpq, tensor_layout=layout)
+        orc = getattr(O, name)(q.cpu(), k.cpu(), km.cpu(), WARPQ=warpq, tensor_layout=layout)
+        for i in (0, 2):
+            dc = (mine[i].cpu().int() - orc[i].int()).abs()
+            assert dc.max().item() <= 1, f"{name}[{i}] code off by more than 1"
+            assert (dc != 0).float().mean().item() <= 1e-3, f"{name}[{i}] too many differing codes"
+        for i in (1, 3):
+            w = orc[i].shape[-1]
+            a, bb = mine[i].cpu()[..., :w], orc[i]
+            nz = bb != 0
+            assert ((a[nz] - bb[nz]).abs() <= bb[nz].abs() * 2.4e-7).all(), f"{name}[{i}] scale beyond 2 ulp"
