@@ -80,7 +80,11 @@ def _quant_groups_triton(xg):
     sageattention/triton/quant_per_thread.py:39-44: scale = max|x|/127 + 1e-7; y = x/scale;
     y += 0.5*sign; truncate."""
     amax = xg.abs().amax(dim=(-1, -2))
-    scale = amax / 127.0 + torch.tensor(1e-7, dtype=torch.float32)
+    # the reference binary evaluates `amax / 127. + 1e-7` as ONE fma with the f32 reciprocal of 127
+    # (ptxas folds Triton's div.full.f32-by-constant + add.f32; see prepass.cu pt_scale).  The f64
+    # product of two f32 values is exact, so rounding the f64 sum to f32 reproduces the fma.
+    rcp127 = torch.tensor([0x3C010204], dtype=torch.int32).view(torch.float32).double()
+    scale = (amax.double() * rcp127 + torch.tensor(1e-7, dtype=torch.float32).double()).float()
     y = xg / scale[..., None, None]
     y = y + torch.where(y >= 0, 0.5, -0.5)
     return torch.trunc(y).to(torch.int8), scale

@@ -52,6 +52,35 @@ SIGNATURES = {
 
 _lib = None
 
+# kernels launched by one call of each entry point (cudaMemsetAsync is not counted); LAUNCHES is
+# bumped on every call so bench.py can report how many of OUR kernels ran in its timed region.
+KERNELS_PER_CALL = {
+    "sage_seq_mean": 1, "sage_quant_int8": 1, "sage_quant_per_thread_int8": 1, "sage_sub_mean": 1,
+    "sage_per_channel_fp8": 2, "sage_attn_i8_f16": 1, "sage_attn_i8_f8": 1,
+}
+LAUNCHES = 0
+
+
+class _Counted:
+    """ctypes function wrapper that counts kernel launches."""
+
+    def __init__(self, fn, n):
+        self._fn, self._n = fn, n
+
+    def __call__(self, *a):
+        global LAUNCHES
+        LAUNCHES += self._n
+        return self._fn(*a)
+
+
+class _LibView:
+    def __init__(self, lib):
+        self._lib = lib
+        for name in SIGNATURES:
+            fn = getattr(lib, name)
+            n = KERNELS_PER_CALL.get(name)
+            setattr(self, name, _Counted(fn, n) if n else fn)
+
 
 def load():
     """Load (building first if needed) and return the ctypes library handle."""
@@ -66,8 +95,8 @@ def load():
         fn = getattr(lib, name)  # AttributeError if the symbol is missing: fail loudly
         fn.restype = res
         fn.argtypes = args
-    _lib = lib
-    return lib
+    _lib = _LibView(lib)
+    return _lib
 
 
 def check(rc):

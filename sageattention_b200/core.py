@@ -19,6 +19,10 @@ from .quant import (_dims, _dtype_code, _require_cuda, _stream, per_channel_fp8,
 
 _LOG2E = 1.44269504
 
+# bench.py sets this to a list to collect (start, end) CUDA events around every attention-kernel
+# launch (the roofline's "dominant kernel" duration); None = no events recorded.
+KERNEL_EVENTS = None
+
 
 def _pad_head_dim(q, k, v):
     """Zero-pad head_dim to 64 / 128 like core.py:590-601."""
@@ -97,7 +101,14 @@ def _launch(fp8, q_int8, k_int8, v, o, q_scale, k_scale, v_scale, v_mean, tensor
     a.debug_s = debug_s.data_ptr() if debug_s is not None else None
     fn = lib.sage_attn_i8_f8 if fp8 else lib.sage_attn_i8_f16
     with torch.cuda.device(o.device):
-        _lib.check(fn(a, _stream(o)))
+        if KERNEL_EVENTS is not None:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            _lib.check(fn(a, _stream(o)))
+            e1.record()
+            KERNEL_EVENTS.append((e0, e1))
+        else:
+            _lib.check(fn(a, _stream(o)))
     return lse
 
 

@@ -89,6 +89,11 @@ def test_f16_kernel_vs_reference_sm80(ref_sm80, case, gran):
     o, lse = run_kernel("f16", q8, qs, k8, ks, v, None, None, g, causal, sm, dtype, lse=True)
     ro = torch.empty_like(o)
     rlse = ref_sm80.qk_int8_sv_f16_accum_f32_attn(q8, k8, v, ro, qs, ks, 1, int(causal), g, sm, 1)
+    assert torch.isfinite(o).all()
+    if not torch.isfinite(ro).all():
+        # the reference does not zero-fill out-of-range V rows of the last tile (kNoFill,
+        # /root/reference/csrc/qattn/attn_utils.cuh:130): 0 * uninitialised shared memory can be NaN
+        pytest.skip("reference kernel produced non-finite values from uninitialised shared memory")
     cos, l1, _ = accuracy(o, ro)
     assert cos >= 0.9999 and l1 <= 1e-2, (cos, l1)
     assert (lse - rlse).abs().max().item() <= 2e-3
