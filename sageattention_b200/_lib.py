@@ -10,7 +10,7 @@ import ctypes
 import os
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
-_LIB_PATH = os.path.join(_PKG, "libsage_b200.so")
+_LIB_PATH = os.environ.get("SAGE_B200_LIB") or os.path.join(_PKG, "libsage_b200.so")  # env: kernel-variant A/B runs
 
 c_i64 = ctypes.c_int64
 c_int = ctypes.c_int

@@ -45,7 +45,9 @@ constexpr int kKStages = 2;
 constexpr int kVStages = 2;
 constexpr int kSoftmaxThreads = 256;  // 2 warpgroups
 constexpr int kThreads = 320;         // + TMA warp + MMA warp
-constexpr float kFp8Offset = 8.807f;  // log2(448) rounded down, as the reference (attn_utils.cuh:30)
+constexpr float kFp8Tau = 2.0f;
+constexpr float kF16Tau = 8.0f;
+constexpr float kFp8Offset = 8.807f - kFp8Tau;  // log2(448) rounded down, as the reference (attn_utils.cuh:30)
 constexpr float kMagicF = 12582912.0f;  // 1.5 * 2^23
 constexpr int kMagicI = 0x4B400000;
 constexpr int kMaskedS = -4194304;  // below any reachable int8 dot product (|S| <= 2^21)
@@ -128,8 +130,13 @@ __device__ __forceinline__ void softmax_row(uint32_t (&s)[128], const float (&sc
     if constexpr (kMasked) cand = (mx[k] == kMaskedS) ? -1e30f : cand;
     mrow = fmaxf(mrow, cand);
   }
-  const float m_new = fmaxf(m_run, mrow);
-  alpha = ex2_approx(m_run - m_new);  // 0 on the first tile (m_run = -1e30)
+  const bool grow = mrow > m_run + (kFp8 ? kFp8Tau : kF16Tau);
+  float m_new = m_run;
+  alpha = 1.0f;
+  if (__any_sync(0xffffffffu, grow)) {
+    m_new = fmaxf(m_run, mrow);
+    alpha = ex2_approx(m_run - m_new);  // 0 on the first tile (m_run = -1e30)
+  }
   m_run = m_new;
   float bias[8];
 #pragma unroll

@@ -39,29 +39,30 @@ __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t by
                "r"(bytes)
                : "memory");
 }
-__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+// try_wait suspends the warp in hardware for up to `hint_ns` before it reports failure, so a waiting
+// warp costs (almost) no issue slots.
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity, uint32_t hint_ns = 20000) {
   uint32_t ok;
   asm volatile(
       "{\n\t.reg .pred P;\n\t"
-      "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 P, [%1], %2, %3;\n\t"
       "selp.u32 %0, 1, 0, P;\n\t}\n"
       : "=r"(ok)
-      : "r"(smem_u32(bar)), "r"(parity)
+      : "r"(smem_u32(bar)), "r"(parity), "r"(hint_ns)
       : "memory");
   return ok != 0;
 }
-// Bounded spin: a lost arrival traps (reported as a launch failure) instead of hanging the GPU.
+// Bounded wait: a lost arrival traps (reported as a launch failure) instead of hanging the GPU.
 #ifndef SAGE_MBAR_SPIN_LIMIT
-#define SAGE_MBAR_SPIN_LIMIT (1u << 24)
+#define SAGE_MBAR_SPIN_LIMIT (1u << 20)
 #endif
+// (no printf here: a call in the wait path would force every live register of the softmax loop
+// to be spilled around it)
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return;  // fast path: already complete
   uint32_t spins = 0;
   while (!mbar_try_wait(bar, parity)) {
-    if (++spins > SAGE_MBAR_SPIN_LIMIT) {
-      printf("sage: mbarrier timeout blk(%d,%d,%d) thr %d bar@%u parity %u\n", blockIdx.x,
-             blockIdx.y, blockIdx.z, threadIdx.x, smem_u32(bar), parity);
-      __trap();
-    }
+    if (++spins > SAGE_MBAR_SPIN_LIMIT) __trap();
   }
 }
 
@@ -199,6 +200,16 @@ __device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&r)[16
       "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]),
       "r"(r[8]), "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
       : "memory");
+}
+
+// register re-distribution between warpgroups (all 4 warps of a warpgroup must execute it)
+template <int kRegs>
+__device__ __forceinline__ void reg_alloc() {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;\n" ::"n"(kRegs));
+}
+template <int kRegs>
+__device__ __forceinline__ void reg_dealloc() {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" ::"n"(kRegs));
 }
 
 // named barrier among a subset of warps
