@@ -75,7 +75,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "50"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.t = threading.Thread(target=self._read, daemon=True)
             self.t.start()
@@ -119,7 +119,7 @@ def cpu_sample(api, b, h, n, d, causal, dtype_name, budget_s=20.0):
     torch.set_num_threads(os.cpu_count() or 1)
     dtype = getattr(torch, dtype_name)
     pv = "f16" if "fp16" in api else "f8"
-    hs = min(h, 2)
+    hs = min(h, 8)
     ns = min(n, 4096)
     g = torch.Generator().manual_seed(0)
     q = torch.randn(1, hs, ns, d, generator=g).to(dtype)
@@ -132,7 +132,7 @@ def cpu_sample(api, b, h, n, d, causal, dtype_name, budget_s=20.0):
         O.sageattn_ref(q, k, v, pv=pv, is_causal=causal, **kw)
         reps += 1
         el = time.perf_counter() - t0
-        if el > budget_s or reps >= 3:
+        if el > budget_s or reps >= 20:
             break
     t = el / reps
     tops = flops_of(1, hs, ns, d, causal) / t * 1e-12
@@ -171,7 +171,7 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2_fp16", choices=sorted(WORKLOADS))

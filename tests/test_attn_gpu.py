@@ -5,8 +5,11 @@ the reference API) against
       same codes - the north-star's GPU oracle,
   (c) fp32 scaled_dot_product_attention end to end.
 Tolerances (floating point, so not bit-exact): kernel-vs-kernel on identical quantised inputs
-cos >= 0.9999 and rel-L1 <= 1e-2 (fp16 PV) / 2e-2 (fp8 PV: P is re-rounded to e4m3 in a different
-tile order); end-to-end vs fp32 SDPA cos >= 0.999 and a rel-L1 no worse than 1.15x what the oracle
+cos >= 0.9999 and rel-L1 <= 1e-2 for fp16 PV.  For fp8 PV both kernels round P to e4m3 (3 mantissa
+bits) relative to DIFFERENT reference maxima (ours keeps a lazily updated one), so the two sets of
+rounding errors are independent: the pairwise gate is cos >= 0.9995 / rel-L1 <= 3e-2, and the
+meaningful gate is the distance to the fp64 result computed from the same codes, where ours must be
+within 1.10x of the reference algorithm's own error.  End-to-end vs fp32 SDPA cos >= 0.999 and a rel-L1 no worse than 1.15x what the oracle
 restatement of the reference algorithm itself achieves on the same input.
 """
 import pytest
@@ -15,7 +18,7 @@ import torch
 import sageattention_b200 as sb
 from sageattention_b200 import _lib, core
 from oracle import sage_oracle as O
-from conftest import accuracy
+from conftest import accuracy, exact_attention_from_codes
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
@@ -69,10 +72,15 @@ def test_kernel_vs_cpu_oracle_same_codes(case, pv, gran):
                            v_scale=None if vs is None else vs.cpu(), gran=g, is_causal=causal,
                            sm_scale=sm, return_lse=True, out_dtype=dtype)
     cos, l1, _ = accuracy(o.cpu(), oo)
-    assert cos >= 0.9999, (cos, l1)
-    assert l1 <= (2e-2 if pv == "f8" else 1e-2), (cos, l1)
+    assert cos >= (0.9995 if pv == "f8" else 0.9999), (cos, l1)
+    assert l1 <= (3e-2 if pv == "f8" else 1e-2), (cos, l1)
     assert (lse.cpu() - olse).abs().max().item() <= 2e-3
     assert torch.isfinite(o).all()
+    exact, elog2 = exact_attention_from_codes(q8, k8, vq, qs, ks, g, causal, sm, v_scale=vs)
+    _, l1_mine, _ = accuracy(o, exact)
+    _, l1_orc, _ = accuracy(oo.to(DEV), exact)
+    assert l1_mine <= 1.10 * l1_orc + 1e-4, (l1_mine, l1_orc)
+    assert (lse.double() - elog2).abs().max().item() <= 2e-3
 
 
 @pytest.mark.parametrize("case", CASES)
@@ -115,8 +123,12 @@ def test_f8_kernel_vs_reference_sm89(ref_sm89, case, gran):
     ro = torch.empty_like(o)
     rlse = ref_sm89.qk_int8_sv_f8_accum_f32_fuse_v_scale_attn(q8, k8, vq, ro, qs, ks, vs, 1, int(causal), g, sm, 1)
     cos, l1, _ = accuracy(o, ro)
-    assert cos >= 0.9999 and l1 <= 2e-2, (cos, l1)
+    assert cos >= 0.9995 and l1 <= 3e-2, (cos, l1)
     assert (lse - rlse).abs().max().item() <= 2e-3
+    exact, _ = exact_attention_from_codes(q8, k8, vq, qs, ks, g, causal, sm, v_scale=vs)
+    _, l1_mine, _ = accuracy(o, exact)
+    _, l1_ref, _ = accuracy(ro, exact)
+    assert l1_mine <= 1.10 * l1_ref + 1e-4, (l1_mine, l1_ref)
 
 
 @pytest.mark.parametrize("fn,kw", [

@@ -1,8 +1,10 @@
 """GPU: the sm_100a library (through the C ABI) against the golden fixtures - outputs of the
 reference's own compiled kernels (tests/golden/make_golden.py).  Codes and scales: BIT-EXACT.
 Attention outputs (floating point, different tile order and f32 accumulation in TMEM):
-cos >= 0.9999, rel-L1 <= 5e-3 (fp16 PV vs the sm80 kernel) / 2e-2 (fp8 PV vs the sm89 kernel),
-LSE within 2e-3."""
+cos >= 0.9999, rel-L1 <= 5e-3 (fp16 PV vs the sm80 kernel); fp8 PV vs the sm89 kernel: both round P
+to e4m3 against different reference maxima (independent rounding errors), so cos >= 0.9995,
+rel-L1 <= 3e-2 pairwise AND our distance to the fp64 result from the same codes must be within
+1.10x of the reference kernel's own; LSE within 2e-3."""
 import glob
 import os
 
@@ -11,7 +13,7 @@ import torch
 
 import sageattention_b200 as sb
 from sageattention_b200 import core
-from conftest import accuracy
+from conftest import accuracy, exact_attention_from_codes
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
@@ -74,5 +76,10 @@ def test_attention_vs_golden_reference_kernels(path):
                            causal, gran, 32, sm, True)
         ro, rlse = g[f"sm89_f32_{key}"]
         cos, l1, _ = accuracy(o.cpu(), ro)
-        assert cos >= 0.9999 and l1 <= 2e-2, (key, cos, l1)
+        assert cos >= 0.9995 and l1 <= 3e-2, (key, cos, l1)
         assert (lse.cpu() - rlse).abs().max().item() <= 2e-3
+        exact, _ = exact_attention_from_codes(q8, k8, v8u.to(DEV).view(torch.float8_e4m3fn), qs, ks, gran, causal,
+                                              sm, v_scale=vs.to(DEV))
+        _, l1_mine, _ = accuracy(o, exact)
+        _, l1_ref, _ = accuracy(ro.to(DEV), exact)
+        assert l1_mine <= 1.10 * l1_ref + 1e-4, (key, l1_mine, l1_ref)
