@@ -41,6 +41,9 @@ WORKLOADS = {
     "hunyuan": ("sageattn", 1, 24, 119056, 128, False, "bfloat16"),
     "wan": ("sageattn", 1, 40, 75600, 128, False, "bfloat16"),
 }
+# dram__bytes_read.sum + dram__bytes_write.sum of the attention kernel, one `ncu --set full` capture
+# per workload (profiles/r1_ncu_attn_f16_c2_summary.txt); algorithmic bytes at C2 fp16 = 402.7e6
+NCU_TRAFFIC = {"c2_fp16": 375.85e6}
 METRIC = "attention TOPS @hd64/hd128 seq 1K-32K (causal/non-causal), % of INT8/FP8 tensor peak"
 
 
@@ -299,7 +302,7 @@ def main():
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                     "frac": achieved / peak, "traffic": None, "kernel": "sage_attn_fwd_kernel",
+                     "frac": achieved / peak, "traffic": NCU_TRAFFIC.get(args.workload), "kernel": "sage_attn_fwd_kernel",
                      "kernel_ms": kern_ms_avg,
                      "peak_basis": f"{basis} bf16 cuBLAS {bf16_peak:.0f} TF/s x {mix:.3f} (i8/fp8 MMAs run at 2x the f16 rate); "
                                    f"nominal {'4500' if fp8 else '3000'}",
