@@ -180,6 +180,8 @@ def main():
     ap.add_argument("--workload", default="c2_fp16", choices=sorted(WORKLOADS))
     ap.add_argument("--no-sweep", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--sp", default="heads", choices=["heads", "ulysses"],
+                    help="DiT workloads under torchrun: head sharding (no collective) or Ulysses all-to-all")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
@@ -212,9 +214,21 @@ def main():
         h_loc = h
         scaling = "weak"
     torch.manual_seed(rank)
-    q = torch.randn(b, h_loc, n, d, dtype=dtype, device=dev)
-    k = torch.randn(b, h_loc, n, d, dtype=dtype, device=dev)
-    v = torch.randn(b, h_loc, n, d, dtype=dtype, device=dev)
+    ulysses = sharded and args.sp == "ulysses"
+    if ulysses:
+        # sequence-sharded activations [B, N/P, H, D]; the sequence is padded to a multiple of P
+        from sageattention_b200 import parallel
+        n_loc = (n + world - 1) // world
+        shape = (b, n_loc, h, d)
+        base_fn = fn
+        fn = lambda q_, k_, v_, is_causal=False: parallel.ulysses_sageattn(q_, k_, v_, attn_fn=base_fn,
+                                                                           is_causal=is_causal)
+        n = n_loc * world
+    else:
+        shape = (b, h_loc, n, d)
+    q = torch.randn(shape, dtype=dtype, device=dev)
+    k = torch.randn(shape, dtype=dtype, device=dev)
+    v = torch.randn(shape, dtype=dtype, device=dev)
     flops_rank = flops_of(b, h_loc, n, d, causal)
     flops_job = flops_rank * world
 
@@ -255,8 +269,8 @@ def main():
     value = flops_job / (t_ms * 1e-3) * 1e-12
 
     # ---------------- end to end with host buffers
-    qh, kh, vh = (torch.randn(b, h_loc, n, d, dtype=dtype).pin_memory() for _ in range(3))
-    oh = torch.empty(b, h_loc, n, d, dtype=dtype).pin_memory()
+    qh, kh, vh = (torch.randn(shape, dtype=dtype).pin_memory() for _ in range(3))
+    oh = torch.empty(shape, dtype=dtype).pin_memory()
     qd, kd, vd = (torch.empty_like(q) for _ in range(3))
 
     def e2e_step():
@@ -295,7 +309,7 @@ def main():
         "ms_per_step": t_ms, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
         "dtype": "int8+fp8" if fp8 else "int8+fp16", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {api} B={b} H={h} N={n} D={d} causal={causal} {dtype_name}, "
-                               f"heads per rank {h_loc}",
+                               f"heads per rank {h_loc}" + (", Ulysses all-to-all (NCCL)" if ulysses else ""),
                    "l2": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2" % (4 * nbytes / 1e6)},
         "e2e": {"value": e2e_val, "unit": "TOPS", "h2d_bytes_per_step": 3 * nbytes * world,
                 "d2h_bytes_per_step": nbytes * world, "ms_per_step": e2e_ms},

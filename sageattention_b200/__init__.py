@@ -4,6 +4,7 @@ Exports the same names as /root/reference/sageattention/__init__.py, as real dis
 (the fork aliases them all to one implementation, __init__.py:59-95).
 """
 from .core import sageattn, sageattn_qk_int8_pv_fp16_cuda, sageattn_qk_int8_pv_fp8_cuda
+from .parallel import shard_heads, ulysses_sageattn
 from .quant import per_block_int8, per_channel_fp8, per_thread_int8, per_warp_int8, seq_mean, sub_mean
 
 # the reference's sm90 entry point has the same contract as the fp8 one; on sm_100a both are the
@@ -21,4 +22,6 @@ __all__ = [
     "sub_mean",
     "per_channel_fp8",
     "seq_mean",
+    "ulysses_sageattn",
+    "shard_heads",
 ]

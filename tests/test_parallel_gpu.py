@@ -1,0 +1,53 @@
+"""GPU, 2 ranks over NCCL (skipped on a 1-GPU box): Ulysses sageattn on sequence-sharded inputs
+equals the single-GPU operator on the gathered inputs BIT FOR BIT (same heads, same full sequence,
+same kernels), and is within the operator's tolerance of fp32 SDPA."""
+import os
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+pytestmark = pytest.mark.gpu
+
+
+def _worker(rank, world, port, q_out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        import sageattention_b200 as sb
+        from sageattention_b200 import parallel
+        g = torch.Generator().manual_seed(0)
+        b, n, h, d = 1, 1024, 8, 128
+        q, k, v = (torch.randn(b, n, h, d, generator=g).to(torch.bfloat16).cuda() for _ in range(3))
+        full = sb.sageattn(q, k, v, tensor_layout="NHD")
+        nl = n // world
+        sl = slice(rank * nl, (rank + 1) * nl)
+        o = parallel.ulysses_sageattn(q[:, sl].contiguous(), k[:, sl].contiguous(), v[:, sl].contiguous())
+        torch.cuda.synchronize()
+        same = torch.equal(o, full[:, sl])
+        ref = torch.nn.functional.scaled_dot_product_attention(q.float().transpose(1, 2), k.float().transpose(1, 2),
+                                                               v.float().transpose(1, 2)).transpose(1, 2)[:, sl]
+        cos = torch.nn.functional.cosine_similarity(o.float().flatten(), ref.flatten(), dim=0).item()
+        q_out.put((rank, same, cos))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_ulysses_two_gpus_matches_single_gpu():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    ctx = mp.get_context("spawn")
+    q_out = ctx.Queue()
+    port = 29700 + os.getpid() % 1000
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, q_out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q_out.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, same, cos in res:
+        assert same, f"rank {rank}: Ulysses output differs from the single-GPU operator"
+        assert cos >= 0.999
