@@ -9,16 +9,17 @@
 //     sequence in 128-row tiles;
 //   * warp 8 is the TMA producer (Q once, then a K ring and a V ring, 128B-swizzled smem);
 //   * warp 9 is the single-thread MMA issuer:  S_t = Q_t.K^T  as tcgen05.mma kind::i8 (s32 in TMEM),
-//     O_t += P_t.V as kind::f8f6f4 (e4m3) or kind::f16 with the A operand (P) read from TMEM;
+//     O_t += P_t.V as kind::f8f6f4 (e4m3) or kind::f16, P read from shared memory;
 //   * warps 0-3 / 4-7 are two softmax warpgroups, one per Q tile, one thread per query row:
-//     tcgen05.ld S -> dequant (q/k scales) -> running max / exp2 / row-sum -> P packed to
-//     e4m3/f16 and written back over S in TMEM with tcgen05.st; they also rescale O in TMEM when
-//     a row maximum moves, and run the epilogue (1/d, v_scale, v_mean, cast, store, LSE).
-//   The issue order  PV0(j) S0(j+1) PV1(j) S1(j+1)  staggers the two warpgroups so the tensor
-//   pipe works for one tile while the other tile is in softmax.
+//     tcgen05.ld S (whole row to registers, which frees S_t at once) -> dequant (q/k scales) ->
+//     running max / exp2 / row-sum -> P packed to e4m3/f16 and written to a 128B-swizzled smem tile;
+//     they also rescale O in TMEM when a row maximum moves by more than tau, and run the epilogue
+//     (1/d, v_scale, v_mean, cast, store, LSE).
+//   Because P does not alias S, the issuer launches S_t(j+1) as soon as warpgroup t has drained
+//   S_t(j): the QK MMA runs under that warpgroup's own softmax and the warpgroups never wait for
+//   the tensor pipe in steady state (measured: tools/trace_attn.py).
 //
-// TMEM map (512 columns):  S0 [0,128)  S1 [128,256)  O0 [256,256+D)  O1 [256+D,256+2D);
-// P_t aliases the first 32 (e4m3) / 64 (f16) columns of S_t.
+// TMEM map (512 columns):  S0 [0,128)  S1 [128,256)  O0 [256,256+D)  O1 [256+D,256+2D).
 //
 // Numerics contract (tolerance-checked against the reference kernels and fp32 SDPA):
 //   s' = S * q_scale * k_scale * sm_scale * log2(e);  m = running row max;  p = ex2(s' - m [+8.807]);
@@ -40,12 +41,28 @@
 
 namespace sage {
 
+// Development aid (-DSAGE_TRACE, tools/trace_attn.py): SM-clock stamps of CTA (0,0,0)'s pipeline.
+#ifdef SAGE_TRACE
+constexpr int kTraceSteps = 48, kTraceSlots = 8;
+__device__ long long g_trace[3][kTraceSteps][kTraceSlots];
+#define SAGE_STAMP(who, j, slot)                                                             \
+  do {                                                                                       \
+    if (trace_on && (j) < kTraceSteps) g_trace[who][j][slot] = clock64();                    \
+  } while (0)
+#else
+#define SAGE_STAMP(who, j, slot) do { } while (0)
+#endif
+
 constexpr int kTileQ = 128;       // rows per Q tile (= TMEM lanes)
 constexpr int kTileKV = 128;      // kv rows per step
 constexpr int kKStages = 2;
 constexpr int kVStages = 2;
 constexpr int kSoftmaxThreads = 256;  // 2 warpgroups
-constexpr int kThreads = 320;         // + TMA warp + MMA warp
+constexpr int kThreads = 384;         // + a third warpgroup: TMA warp, MMA warp, two idle warps
+// setmaxnreg: the launch gives every warp 168 registers; the third warpgroup hands most of its
+// share to the softmax warpgroups, whose exp loop needs the headroom to keep many logits in flight.
+constexpr int kSoftmaxRegs = 232;
+constexpr int kIssueRegs = 40;
 struct AttnKernelParams {
   const float* q_scale;
   const float* k_scale;
@@ -72,8 +89,10 @@ struct SmemLayout {
   static constexpr int kQOff = 0;
   static constexpr int kKOff = kQOff + 2 * kQBytes;
   static constexpr int kVOff = kKOff + kKStages * kKBytes;
-  static constexpr int kBarOff = kVOff + kVStages * kVBytes;
-  static constexpr int kNumBars = 1 + 2 * kKStages + 2 * kVStages + 2 + 2 + 2;
+  static constexpr int kPBytes = kFp8 ? kTileQ * kTileKV : kTileQ * kTileKV * 2;  // K-major, SW128
+  static constexpr int kPOff = kVOff + kVStages * kVBytes;
+  static constexpr int kBarOff = kPOff + 2 * kPBytes;
+  static constexpr int kNumBars = 1 + 2 * kKStages + 2 * kVStages + 5 * 2;
   static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
   static constexpr int kTotal = kTmemPtrOff + 16;
   static constexpr int kDynamic = kTotal + 1024;  // slack for 1024B alignment
@@ -83,8 +102,10 @@ struct SmemLayout {
 template <int D, bool kFp8>
 __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int t, int row,
                                                   int q_tile_start, int n_iter, int b, int h,
-                                                  int hkv, uint32_t tmem_base, uint64_t* s_full,
-                                                  uint64_t* p_full, uint64_t* o_full) {
+                                                  int hkv, uint32_t tmem_base, uint8_t* p_smem,
+                                                  uint64_t* s_full, uint64_t* s_free,
+                                                  uint64_t* p_full, uint64_t* p_empty,
+                                                  uint64_t* o_full, int n_pingpong) {
   const int warp_in_wg = (row >> 5);
   const uint32_t lane_off = (uint32_t)(warp_in_wg * 32) << 16;
   const uint32_t tS = tmem_base + lane_off + (uint32_t)(t * 128);
@@ -104,6 +125,13 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
   const float* ksp = p.k_scale + (size_t)(b * p.Hkv + hkv) * p.k_scale_per_bh;
 
   float m_run = -1e30f, d_run = 0.f;
+  // named barrier 1: "warpgroup 0 may start exp" (first pass granted here by warpgroup 1),
+  // named barrier 2: "warpgroup 1 may start exp".  Only the first n_pingpong steps, which both
+  // warpgroups execute, take part.
+  if (t == 1 && n_pingpong > 0) named_bar_arrive(1, 2 * kTileQ);
+#ifdef SAGE_TRACE
+  const bool trace_on = (blockIdx.x | blockIdx.y | blockIdx.z) == 0 && row == 0;
+#endif
 
   for (int j = 0; j < n_iter; ++j) {
     // k scales of this tile -> 8 class scales
@@ -117,8 +145,10 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
       idx = min(idx, p.k_scale_per_bh - 1);
       sc[k] = __ldg(ksp + idx) * qs;
     }
+    SAGE_STAMP(t, j, 0);
     mbar_wait(&s_full[t], j & 1);
     tc_fence_after();
+    SAGE_STAMP(t, j, 1);
     uint32_t s[128];
     {
       uint32_t(&s0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
@@ -131,6 +161,10 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
       tmem_ld32(tS + 96, s3);
       tc_wait_ld();
     }
+    // S_t is in registers: the issuer may overwrite it with S_t(j+1)
+    tc_fence_before();
+    mbar_arrive(&s_free[t]);
+    SAGE_STAMP(t, j, 2);
     if (p.debug_s != nullptr && j == 0) {
       const int nq_pad = (p.Nq + 255) / 256 * 256;
       int* dst = p.debug_s + ((size_t)(b * p.Hq + h) * nq_pad + q_row) * 128;
@@ -141,35 +175,54 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
     int lim = p.Nk - 1 - kv0;
     if (p.causal) lim = min(lim, q_row - kv0);
     const bool masked_tile = (j == n_iter - 1) && (p.causal || (p.Nk - kv0) < kTileKV);
-    float alpha;
+    float alpha, bias[8], dsum;
     uint32_t w[kFp8 ? 32 : 64];
-    if (masked_tile) softmax_row<kFp8, true>(s, sc, lim, m_run, d_run, alpha, w);
-    else softmax_row<kFp8, false>(s, sc, 127, m_run, d_run, alpha, w);
-
-    // rescale O when some row of this warp moved its max (PV(j-1) is complete: S(j) was issued
-    // after it and tcgen05.commit tracks all earlier MMAs)
-    if (j > 0 && __any_sync(0xffffffffu, alpha != 1.0f)) {
+    if (masked_tile) softmax_max<kFp8, true>(s, sc, lim, m_run, alpha, bias);
+    else softmax_max<kFp8, false>(s, sc, 127, m_run, alpha, bias);
+    // The exp phases of the two warpgroups alternate (they are the only MUFU-bound stretch): each
+    // warpgroup's load / max / pack / store phases then run under the other one's exponentials.
+    SAGE_STAMP(t, j, 5);
+    if (j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
+    SAGE_STAMP(t, j, 6);
+    if (masked_tile) dsum = softmax_exp<true>(s, sc, bias, lim);
+    else dsum = softmax_exp<false>(s, sc, bias, 127);
+    if (j < n_pingpong - t) named_bar_arrive(2 - t, 2 * kTileQ);
+    SAGE_STAMP(t, j, 7);
+    d_run = fmaf(d_run, alpha, dsum);
+    softmax_pack<kFp8>(s, w);
+    SAGE_STAMP(t, j, 3);
+    // PV(j-1) complete: P tile reusable and O_t stable
+    if (j > 0) {
+      mbar_wait(&p_empty[t], (j - 1) & 1);
+      // rescale O when some row of this warp moved its max
+      if (__any_sync(0xffffffffu, alpha != 1.0f)) {
+        tc_fence_after();
 #pragma unroll
-      for (int c0 = 0; c0 < D; c0 += 32) {
-        uint32_t o[32];
-        tmem_ld32(tO + c0, o);
-        tc_wait_ld();
+        for (int c0 = 0; c0 < D; c0 += 32) {
+          uint32_t o[32];
+          tmem_ld32(tO + c0, o);
+          tc_wait_ld();
 #pragma unroll
-        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-        tmem_st32(tO + c0, o);
+          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+          tmem_st32(tO + c0, o);
+        }
+        tc_wait_st();
+        tc_fence_before();
       }
     }
-    if constexpr (kFp8) {
-      tmem_st32(tS, w);
-    } else {
-      uint32_t(&w0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&w[0]);
-      uint32_t(&w1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&w[32]);
-      tmem_st32(tS, w0);
-      tmem_st32(tS + 32, w1);
+    // P row -> smem, K-major 128B-swizzled (16B chunk c of row r sits at chunk c ^ (r & 7))
+    {
+      const uint32_t prow = smem_u32(p_smem) + (uint32_t)row * 128u;
+      const uint32_t x = (uint32_t)(row & 7);
+#pragma unroll
+      for (int c = 0; c < (kFp8 ? 8 : 16); ++c) {
+        const uint32_t addr = prow + (uint32_t)(c >> 3) * (kTileQ * 128) + (((uint32_t)(c & 7) ^ x) << 4);
+        st_shared_v4(addr, w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
+      }
     }
-    tc_wait_st();
-    tc_fence_before();
+    fence_proxy_async_smem();
     mbar_arrive(&p_full[t]);
+    SAGE_STAMP(t, j, 4);
   }
 
   // ---- epilogue
@@ -235,8 +288,10 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   uint64_t* v_full = k_empty + kKStages;      // kVStages
   uint64_t* v_empty = v_full + kVStages;      // kVStages
   uint64_t* s_full = v_empty + kVStages;      // 2
-  uint64_t* p_full = s_full + 2;              // 2
-  uint64_t* o_full = p_full + 2;              // 2
+  uint64_t* s_free = s_full + 2;              // 2
+  uint64_t* p_full = s_free + 2;              // 2
+  uint64_t* p_empty = p_full + 2;             // 2
+  uint64_t* o_full = p_empty + 2;             // 2
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(smem + L::kTmemPtrOff);
 
   const int warp = threadIdx.x >> 5;
@@ -264,7 +319,9 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     for (int i = 0; i < kVStages; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
     for (int t = 0; t < 2; ++t) {
       mbar_init(&s_full[t], 1);
+      mbar_init(&s_free[t], kTileQ);
       mbar_init(&p_full[t], kTileQ);
+      mbar_init(&p_empty[t], 1);
       mbar_init(&o_full[t], 1);
     }
     fence_barrier_init();
@@ -284,13 +341,16 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
 
   if (warp < 8) {
     // ======================= softmax warpgroups =======================
+    reg_alloc<kSoftmaxRegs>();
     const int t = warp >> 2;
     const int row = threadIdx.x & 127;
     if (n_it[t] > 0)
       softmax_warpgroup<D, kFp8>(p, t, row, q_start + t * kTileQ, n_it[t], b, h, hkv, tmem_base,
-                                 s_full, p_full, o_full);
+                                 smem + L::kPOff + t * L::kPBytes, s_full, s_free, p_full, p_empty,
+                                 o_full, min(n_it[0], n_it[1]));
   } else if (warp == 8) {
     // ======================= TMA producer =======================
+    reg_dealloc<kIssueRegs>();
     if (elect_one()) {
       mbar_arrive_expect_tx(q_full, 2 * L::kQBytes);
       tma_load_4d(smem + L::kQOff, &tmQ, q_full, 0, q_start, h, b);
@@ -314,8 +374,9 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         }
       }
     }
-  } else {
+  } else if (warp == 9) {
     // ======================= MMA issuer =======================
+    reg_dealloc<kIssueRegs>();
     if (elect_one()) {
       constexpr uint32_t idesc_qk = make_idesc(CFMT_S32, FMT_S8, FMT_S8, 0, 0, kTileQ, kTileKV);
       constexpr uint32_t idesc_pv =
@@ -338,26 +399,33 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
           mma_i8_ss(tmem_base + t * 128, ad, bd, idesc_qk, kk > 0);
         }
       };
+      const uint32_t sP = smem_u32(smem + L::kPOff);
       auto issue_pv = [&](int t, int j) {
+        const uint32_t a0 = sP + t * L::kPBytes;
         const uint32_t b0 = sV + (j % kVStages) * L::kVBytes;
         const uint32_t d_tmem = tmem_base + 256 + t * D;
-        const uint32_t a_tmem = tmem_base + t * 128;
         if constexpr (kFp8) {
 #pragma unroll
           for (int kk = 0; kk < kTileKV / 32; ++kk) {
+            const uint64_t ad = make_smem_desc(a0 + kk * 32, 16, 1024, SWZ_128B);
             const uint64_t bd = make_smem_desc(b0 + kk * 32, 16, 1024, SWZ_128B);
-            mma_f8_ts(d_tmem, a_tmem + kk * 8, bd, idesc_pv, (j > 0) || (kk > 0));
+            mma_f8_ss(d_tmem, ad, bd, idesc_pv, (j > 0) || (kk > 0));
           }
         } else {
 #pragma unroll
           for (int kk = 0; kk < kTileKV / 16; ++kk) {
+            // A: two 64-wide K blocks of [128 rows][128 B], 16 KB apart, 32 B per MMA inside a block
+            const uint64_t ad = make_smem_desc(a0 + (kk >> 2) * (kTileQ * 128) + (kk & 3) * 32, 16, 1024, SWZ_128B);
             // MN-major B: 16 kv rows x 128 B per MMA = 2 KB step; 64-wide d blocks 16 KB apart
             const uint64_t bd = make_smem_desc(b0 + kk * 2048, kTileKV * 128, 1024, SWZ_128B);
-            mma_f16_ts(d_tmem, a_tmem + kk * 8, bd, idesc_pv, (j > 0) || (kk > 0));
+            mma_f16_ss(d_tmem, ad, bd, idesc_pv, (j > 0) || (kk > 0));
           }
         }
       };
 
+#ifdef SAGE_TRACE
+      const bool trace_on = (blockIdx.x | blockIdx.y | blockIdx.z) == 0;
+#endif
       mbar_wait(q_full, 0);
       mbar_wait(&k_full[0], 0);
       tc_fence_after();
@@ -366,26 +434,40 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       tc_commit(&k_empty[0]);
 
       for (int j = 0; j < n_max; ++j) {
+        // S(j+1) as soon as the warpgroup has drained S(j)
+        if (j + 1 < n_max) {
+          mbar_wait(&k_full[(j + 1) % kKStages], ((j + 1) / kKStages) & 1);
+#pragma unroll
+          for (int t = 0; t < 2; ++t) {
+            if (j + 1 < n_it[t]) {
+              SAGE_STAMP(2, j, t * 4 + 0);
+              mbar_wait(&s_free[t], j & 1);
+              tc_fence_after();
+              SAGE_STAMP(2, j, t * 4 + 1);
+              issue_qk(t, j + 1);
+              tc_commit(&s_full[t]);
+            }
+          }
+          tc_commit(&k_empty[(j + 1) % kKStages]);
+        }
         mbar_wait(&v_full[j % kVStages], (j / kVStages) & 1);
-        const bool more = (j + 1 < n_max);
 #pragma unroll
         for (int t = 0; t < 2; ++t) {
           if (j < n_it[t]) {
+            SAGE_STAMP(2, j, t * 4 + 2);
             mbar_wait(&p_full[t], j & 1);
             tc_fence_after();
+            SAGE_STAMP(2, j, t * 4 + 3);
             issue_pv(t, j);
+            tc_commit(&p_empty[t]);
             if (j == n_it[t] - 1) tc_commit(&o_full[t]);
           }
-          if (t == 1) tc_commit(&v_empty[j % kVStages]);
-          if (t == 0 && more) {
-            mbar_wait(&k_full[(j + 1) % kKStages], ((j + 1) / kKStages) & 1);
-            tc_fence_after();
-          }
-          if (j + 1 < n_it[t]) { issue_qk(t, j + 1); tc_commit(&s_full[t]); }
-          if (t == 1 && more) tc_commit(&k_empty[(j + 1) % kKStages]);
         }
+        tc_commit(&v_empty[j % kVStages]);
       }
     }
+  } else {
+    reg_dealloc<kIssueRegs>();
   }
 
   tc_fence_before();
@@ -519,6 +601,12 @@ static int check_attn_args(const sage_attn_args* a) {
 }
 
 }  // namespace sage
+
+#ifdef SAGE_TRACE
+extern "C" int sage_debug_trace(long long* out) {
+  return (int)cudaMemcpyFromSymbol(out, sage::g_trace, sizeof(sage::g_trace));
+}
+#endif
 
 extern "C" int sage_attn_i8_f8(const sage_attn_args* a, void* stream) {
   int rc = sage::check_attn_args(a);

@@ -32,13 +32,15 @@ __device__ __forceinline__ uint32_t pack_f16x2(float a0, float a1) {
 }
 
 // ------------------------------------------------------------------------------------------
-// One softmax step for one query row: s[] holds the 128 int32 logits of this KV tile on entry and
-// is reused for p.  `lim` = last visible column (127 when nothing is masked).
-// Returns packed P words in w[] (32 words e4m3 / 64 words f16).
+// One softmax step for one query row, in three phases so the caller can schedule them (the exp
+// phase is the only one that needs the MUFU pipe).  s[] holds the 128 int32 logits of this KV tile
+// on entry and is reused for p.  `lim` = last visible column (127 when nothing is masked).
+
+// Phase 1: (masking,) row max, lazy-rescale decision.  Out: m_run updated, alpha (1 when the
+// accumulators keep their scale), bias[] for phase 2.
 template <bool kFp8, bool kMasked>
-__device__ __forceinline__ void softmax_row(uint32_t (&s)[128], const float (&sc)[8], int lim,
-                                            float& m_run, float& d_run, float& alpha,
-                                            uint32_t (&w)[kFp8 ? 32 : 64]) {
+__device__ __forceinline__ void softmax_max(uint32_t (&s)[128], const float (&sc)[8], int lim,
+                                            float& m_run, float& alpha, float (&bias)[8]) {
   if constexpr (kMasked) {
 #pragma unroll
     for (int c = 0; c < 128; ++c)
@@ -66,9 +68,14 @@ __device__ __forceinline__ void softmax_row(uint32_t (&s)[128], const float (&sc
     alpha = ex2_approx(m_run - m_new);  // 0 on the first tile (m_run = -1e30)
   }
   m_run = m_new;
-  float bias[8];
 #pragma unroll
   for (int k = 0; k < 8; ++k) bias[k] = fmaf(-kMagicF, sc[k], (kFp8 ? kFp8Offset : 0.f) - m_new);
+}
+
+// Phase 2: p = 2^(s * sc + bias) in place; returns the row sum of this tile.
+template <bool kMasked>
+__device__ __forceinline__ float softmax_exp(uint32_t (&s)[128], const float (&sc)[8],
+                                             const float (&bias)[8], int lim) {
   float dsum0 = 0.f, dsum1 = 0.f;
 #pragma unroll
   for (int c = 0; c < 128; c += 2) {
@@ -85,7 +92,12 @@ __device__ __forceinline__ void softmax_row(uint32_t (&s)[128], const float (&sc
     s[c] = __float_as_uint(p0);
     s[c + 1] = __float_as_uint(p1);
   }
-  d_run = fmaf(d_run, alpha, dsum0 + dsum1);
+  return dsum0 + dsum1;
+}
+
+// Phase 3: pack p to e4m3 (32 words) / f16 (64 words).
+template <bool kFp8>
+__device__ __forceinline__ void softmax_pack(const uint32_t (&s)[128], uint32_t (&w)[kFp8 ? 32 : 64]) {
   if constexpr (kFp8) {
     // V^T is stored with the reference's 16-token permutation
     // out[j] = in[{0,1,8,9,2,3,10,11,4,5,12,13,6,7,14,15}[j]]  (/root/reference/csrc/fused/fused.cu:284-291),
@@ -103,6 +115,146 @@ __device__ __forceinline__ void softmax_row(uint32_t (&s)[128], const float (&sc
     for (int i = 0; i < 64; ++i)
       w[i] = pack_f16x2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1]));
   }
+}
+
+template <bool kFp8, bool kMasked>
+__device__ __forceinline__ void softmax_row(uint32_t (&s)[128], const float (&sc)[8], int lim,
+                                            float& m_run, float& d_run, float& alpha,
+                                            uint32_t (&w)[kFp8 ? 32 : 64]) {
+  float bias[8];
+  softmax_max<kFp8, kMasked>(s, sc, lim, m_run, alpha, bias);
+  const float dsum = softmax_exp<kMasked>(s, sc, bias, lim);
+  d_run = fmaf(d_run, alpha, dsum);
+  softmax_pack<kFp8>(s, w);
+}
+
+// ------------------------------------------------------------------------------------------
+// Streaming form.  The row is processed in four 32-column chunks against the STALE running max
+// (exactly the numbers softmax_row produces when no row grows by more than tau), so max tracking,
+// exp2, row sum and packing of a chunk are independent instruction streams the scheduler can
+// interleave, and chunk c+1 is in flight from TMEM while chunk c is computed.  The caller redoes the
+// row when softmax_grew() reports growth beyond tau.  Arithmetic is packed (FFMA2 / FADD2) and a
+// compile-time fraction of the exponentials runs as a Cody-Waite polynomial on the FMA pipe.
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};\n" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, float& lo, float& hi) {
+  asm("mov.b64 {%0, %1}, %2;\n" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;\n" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("add.rn.f32x2 %0, %1, %2;\n" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+
+// 2^y for a pair on the FMA pipe: n = round(y), 2^(y-n) by a minimax polynomial on [-0.5, 0.5]
+// (relative error 1.7e-3 at degree 2, 7.5e-5 at degree 3), exponent patched in with a shift-add.
+template <int kDeg>
+__device__ __forceinline__ uint64_t exp2_poly2(uint64_t y2) {
+  float y0, y1;
+  unpack2(y2, y0, y1);
+  y2 = pack2(fmaxf(y0, -125.f), fmaxf(y1, -125.f));
+  const uint64_t r2 = fadd2(y2, pack2(kMagicF, kMagicF));
+  const uint64_t fl2 = fadd2(r2, pack2(-kMagicF, -kMagicF));
+  const uint64_t f2 = ffma2(fl2, pack2(-1.f, -1.f), y2);
+  uint64_t p2;
+  if constexpr (kDeg == 2) {
+    p2 = ffma2(f2, pack2(0.23842119f, 0.23842119f), pack2(0.70343381f, 0.70343381f));
+    p2 = ffma2(p2, f2, pack2(1.00044262f, 1.00044262f));
+  } else {
+    p2 = ffma2(f2, pack2(0.05517084f, 0.05517084f), pack2(0.24260935f, 0.24260935f));
+    p2 = ffma2(p2, f2, pack2(0.69326097f, 0.69326097f));
+    p2 = ffma2(p2, f2, pack2(0.99992818f, 0.99992818f));
+  }
+  float r0, r1, p0, p1;
+  unpack2(r2, r0, r1);
+  unpack2(p2, p0, p1);
+  p0 = __int_as_float(__float_as_int(p0) + (__float_as_int(r0) << 23));
+  p1 = __int_as_float(__float_as_int(p1) + (__float_as_int(r1) << 23));
+  return pack2(p0, p1);
+}
+
+struct SoftmaxConsts {
+  float sc[8];    // log2e * sm_scale * q_scale * k_scale[class]
+  float bias[8];  // offset - m_use - magic * sc[class]
+};
+
+template <bool kFp8>
+__device__ __forceinline__ void softmax_set_bias(SoftmaxConsts& k, float m_use) {
+#pragma unroll
+  for (int i = 0; i < 8; ++i) k.bias[i] = fmaf(-kMagicF, k.sc[i], (kFp8 ? kFp8Offset : 0.f) - m_use);
+}
+
+// One 32-column chunk (kChunk = 0..3 of the 128-wide tile).  kPolyNum of every kPolyDen column
+// pairs take the polynomial.  mx[] = per-class integer maxima, dsum2 = packed partial row sums.
+// w: 8 words e4m3 / 16 words f16.  lim: last visible column of the tile (kMasked only).
+template <bool kFp8, bool kMasked, int kChunk, int kPolyNum, int kPolyDen, int kDeg>
+__device__ __forceinline__ void softmax_chunk(const uint32_t (&s)[32], const SoftmaxConsts& k, int lim,
+                                              int (&mx)[8], uint64_t& dsum2, uint32_t (&w)[kFp8 ? 8 : 16]) {
+  float p[32];
+#pragma unroll
+  for (int i = 0; i < 32; i += 2) {
+    constexpr int kBase = (kChunk >> 1) * 4;
+    const int cls = kBase + ((i & 7) >> 1);
+    int s0 = (int)s[i], s1 = (int)s[i + 1];
+    if constexpr (kMasked) {
+      s0 = (kChunk * 32 + i > lim) ? kMaskedS : s0;
+      s1 = (kChunk * 32 + i + 1 > lim) ? kMaskedS : s1;
+    }
+    mx[cls] = max(mx[cls], max(s0, s1));
+    const uint64_t x2 = pack2(__int_as_float(s0 + kMagicI), __int_as_float(s1 + kMagicI));
+    const uint64_t y2 = ffma2(x2, pack2(k.sc[cls], k.sc[cls]), pack2(k.bias[cls], k.bias[cls]));
+    uint64_t p2;
+    if (((i >> 1) % kPolyDen) < kPolyNum) {
+      p2 = exp2_poly2<kDeg>(y2);
+    } else {
+      float y0, y1;
+      unpack2(y2, y0, y1);
+      p2 = pack2(ex2_approx(y0), ex2_approx(y1));
+    }
+    if constexpr (kMasked) {
+      float p0, p1;
+      unpack2(p2, p0, p1);
+      p0 = (kChunk * 32 + i > lim) ? 0.f : p0;
+      p1 = (kChunk * 32 + i + 1 > lim) ? 0.f : p1;
+      p2 = pack2(p0, p1);
+    }
+    dsum2 = fadd2(dsum2, p2);
+    unpack2(p2, p[i], p[i + 1]);
+  }
+  if constexpr (kFp8) {
+    // same K-index permutation as softmax_row (word q of a 16-group = tokens 2q, 2q+1, 2q+8, 2q+9)
+#pragma unroll
+    for (int g = 0; g < 2; ++g)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int t = g * 16 + 2 * q;
+        w[g * 4 + q] = pack_e4m3x4(p[t], p[t + 1], p[t + 8], p[t + 9]);
+      }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 16; ++i) w[i] = pack_f16x2(p[2 * i], p[2 * i + 1]);
+  }
+}
+
+// Row maximum (dequantised) from the per-class integer maxima; -1e30 when every column is masked.
+template <bool kMasked>
+__device__ __forceinline__ float softmax_rowmax(const int (&mx)[8], const SoftmaxConsts& k) {
+  float mrow = -1e30f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    float cand = (float)mx[i] * k.sc[i];
+    if constexpr (kMasked) cand = (mx[i] == kMaskedS) ? -1e30f : cand;
+    mrow = fmaxf(mrow, cand);
+  }
+  return mrow;
 }
 
 }  // namespace sage

@@ -1,5 +1,5 @@
 """Build a variant of libsage_b200.so from an alternative attention source (development tool):
-    python tools/build_variant.py NAME path/to/attn_variant.cu   ->  tools/_bin/libsage_NAME.so
+    python tools/build_variant.py NAME path/to/attn_variant.cu [extra nvcc flags]  ->  tools/_bin/libsage_NAME.so
 Select it at run time with SAGE_B200_LIB=tools/_bin/libsage_NAME.so."""
 import os, shutil, subprocess, sys
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
@@ -11,7 +11,7 @@ out = os.path.join(ROOT, "tools", "_bin"); os.makedirs(out, exist_ok=True)
 tmp = os.path.join(B.CSRC, f"_variant_{name}.cu"); shutil.copy(src, tmp)
 obj = os.path.join(out, f"attn_{name}.o")
 try:
-    subprocess.check_call([B._nvcc(), "-c", tmp, "-o", obj] + B.ARCH + B.COMMON)
+    subprocess.check_call([B._nvcc(), "-c", tmp, "-o", obj] + B.ARCH + B.COMMON + sys.argv[3:])
 finally:
     os.remove(tmp)
 objs = [os.path.join(B.OBJ, n + ".o") for n, _ in B.UNITS if n != "attn_sm100.cu"] + [obj]
