@@ -129,6 +129,76 @@ __device__ __forceinline__ void softmax_row(uint32_t (&s)[128], const float (&sc
 }
 
 // ------------------------------------------------------------------------------------------
+// Half-row forms (64 columns = one 64-row K block = 4 k-scale classes), used by the kernel's
+// two-threads-per-row layout.  Same arithmetic as above.
+__device__ __forceinline__ constexpr int kcls64(int c) { return (c & 7) >> 1; }
+
+// (masking,) dequantised maximum of the half row; -1e30 when every column is masked.
+template <bool kMasked>
+__device__ __forceinline__ float half_rowmax(uint32_t (&s)[64], const float (&sc)[4], int lim) {
+  if constexpr (kMasked) {
+#pragma unroll
+    for (int c = 0; c < 64; ++c)
+      if (c > lim) s[c] = (uint32_t)kMaskedS;
+  }
+  int mx[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) mx[k] = kMaskedS;
+#pragma unroll
+  for (int c = 0; c < 64; ++c) mx[kcls64(c)] = max(mx[kcls64(c)], (int)s[c]);
+  float m = -1e30f;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    float cand = (float)mx[k] * sc[k];
+    if constexpr (kMasked) cand = (mx[k] == kMaskedS) ? -1e30f : cand;
+    m = fmaxf(m, cand);
+  }
+  return m;
+}
+
+// p = 2^(s * sc + bias) in place; returns the sum.
+template <bool kMasked>
+__device__ __forceinline__ float half_exp(uint32_t (&s)[64], const float (&sc)[4],
+                                          const float (&bias)[4], int lim) {
+  float dsum0 = 0.f, dsum1 = 0.f;
+#pragma unroll
+  for (int c = 0; c < 64; c += 2) {
+    float x0 = __int_as_float((int)s[c] + kMagicI);
+    float x1 = __int_as_float((int)s[c + 1] + kMagicI);
+    float p0 = ex2_approx(fmaf(x0, sc[kcls64(c)], bias[kcls64(c)]));
+    float p1 = ex2_approx(fmaf(x1, sc[kcls64(c + 1)], bias[kcls64(c + 1)]));
+    if constexpr (kMasked) {
+      p0 = (c > lim) ? 0.f : p0;
+      p1 = (c + 1 > lim) ? 0.f : p1;
+    }
+    dsum0 += p0;
+    dsum1 += p1;
+    s[c] = __float_as_uint(p0);
+    s[c + 1] = __float_as_uint(p1);
+  }
+  return dsum0 + dsum1;
+}
+
+// pack to e4m3 (16 words, K index permuted inside 16-groups as in softmax_pack) / f16 (32 words)
+template <bool kFp8>
+__device__ __forceinline__ void half_pack(const uint32_t (&s)[64], uint32_t (&w)[kFp8 ? 16 : 32]) {
+  if constexpr (kFp8) {
+#pragma unroll
+    for (int g = 0; g < 4; ++g)
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int t = g * 16 + 2 * q;
+        w[g * 4 + q] = pack_e4m3x4(__uint_as_float(s[t]), __uint_as_float(s[t + 1]),
+                                   __uint_as_float(s[t + 8]), __uint_as_float(s[t + 9]));
+      }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 32; ++i)
+      w[i] = pack_f16x2(__uint_as_float(s[2 * i]), __uint_as_float(s[2 * i + 1]));
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // Streaming form.  The row is processed in four 32-column chunks against the STALE running max
 // (exactly the numbers softmax_row produces when no row grows by more than tau), so max tracking,
 // exp2, row sum and packing of a chunk are independent instruction streams the scheduler can
