@@ -17,7 +17,8 @@
  *   sage_attn_i8_f16             <- _qattn_sm80.qk_int8_sv_f16_accum_{f32,f16,f16_inst_buf}_attn,
  *                                   ..._fuse_v_mean_attn (csrc/qattn/pybind_sm80.cpp, qk_int_sv_f16_cuda_sm80.cu:674-1379)
  *   sage_attn_i8_f8              <- _qattn_sm89.qk_int8_sv_f8_accum_* (7 variants, csrc/qattn/pybind_sm89.cpp)
- *   sage_prepass_*               <- the whole quantisation prologue of core.py:590-632 / 794-830 fused.
+ *   sage_smooth_quant_k_int8     <- `km = k.mean(dim=seq)` followed by the K half of per_warp_int8 /
+ *                                   per_thread_int8 (sageattention/core.py:611-632), fused in one launch
  */
 #ifndef SAGE_B200_H_
 #define SAGE_B200_H_
@@ -72,6 +73,14 @@ int sage_quant_int8(sage_tensor4 x, const void* mean, sage_tensor4 out, float* s
 int sage_quant_per_thread_int8(sage_tensor4 x, const void* mean, sage_tensor4 out, float* scale,
                                int B, int H, int N, int D, int dtype, int is_key, int tile,
                                void* stream);
+
+/* K smoothing and quantisation in one launch (a thread-block cluster per (b,h) slice reads K once
+ * from HBM): mean_out[b,h,:] = dtype(mean over the sequence), then the codes and scales that
+ * sage_quant_int8(block = 64, mean) (per_thread = 0) or sage_quant_per_thread_int8(is_key = 1, mean)
+ * (per_thread = 1) produce for that mean, bit for bit.
+ * scale: [B,H,scale_per_bh], scale_per_bh >= ceil(N/64) (per_thread = 0) or ceil(N/64)*4. */
+int sage_smooth_quant_k_int8(sage_tensor4 k, void* mean_out, sage_tensor4 out, float* scale, int B, int H,
+                             int N, int D, int dtype, int per_thread, int scale_per_bh, void* stream);
 
 /* out(f16)[b,h,n,d] = half( x - mean ) in the input type's packed arithmetic. */
 int sage_sub_mean(sage_tensor4 x, const void* mean, sage_tensor4 out, int B, int H, int N, int D,

@@ -15,7 +15,7 @@ import torch
 
 from . import _lib
 from .quant import (_dims, _dtype_code, _require_cuda, _stream, per_channel_fp8, per_thread_int8,
-                    per_warp_int8, seq_mean, sub_mean)
+                    per_warp_int8, quant_q_int8, seq_mean, smooth_quant_k_int8, sub_mean)
 
 _LOG2E = 1.44269504
 
@@ -48,24 +48,29 @@ def _check_inputs(q, k, v, qk_quant_gran):
     assert q.dtype == k.dtype == v.dtype, "All tensors must have the same dtype."
 
 
-def _smooth_k(q, k, tensor_layout, return_lse):
-    """km = mean over the sequence (input dtype) and the LSE correction q.km (core.py:611-617).
+def _lse_correction(q, km, tensor_layout):
+    """q . km, the term the smoothing removes from every logit of a row (core.py:613-617).
     With GQA the reference's matmul only broadcasts when Hq == Hkv; here km is expanded per q head."""
-    b, hk, nk, d, _ = _dims(k, tensor_layout)
-    km = seq_mean(k, tensor_layout)  # [B, Hkv, D]
-    lse_correction = None
-    if return_lse:
-        hq = q.size(1) if tensor_layout == "HND" else q.size(2)
-        kmq = km if hq == hk else km.repeat_interleave(hq // hk, dim=1)
-        qh = q if tensor_layout == "HND" else q.transpose(1, 2)
-        lse_correction = torch.matmul(qh, kmq.unsqueeze(-1)).squeeze(-1).to(torch.float32)
-    return km, lse_correction
+    hk = km.size(1)
+    hq = q.size(1) if tensor_layout == "HND" else q.size(2)
+    kmq = km if hq == hk else km.repeat_interleave(hq // hk, dim=1)
+    qh = q if tensor_layout == "HND" else q.transpose(1, 2)
+    return torch.matmul(qh, kmq.unsqueeze(-1)).squeeze(-1).to(torch.float32)
 
 
-def _quantize_qk(q, k, km, qk_quant_gran, tensor_layout, warp_q):
+def _quantize_qk(q, k, smooth_k, qk_quant_gran, tensor_layout, warp_q, return_lse):
+    """The quantisation prologue (core.py:611-632): Q codes, and for K either the fused
+    mean + quantise launch (smooth_k) or the plain quantiser.  Returns the four quantiser outputs
+    and the LSE correction (None unless smooth_k and return_lse)."""
+    if smooth_k:
+        q_int8, q_scale = quant_q_int8(q, qk_quant_gran, WARPQ=warp_q, BLKQ=128, tensor_layout=tensor_layout)
+        k_int8, k_scale, km = smooth_quant_k_int8(k, qk_quant_gran, tensor_layout)
+        return q_int8, q_scale, k_int8, k_scale, (_lse_correction(q, km, tensor_layout) if return_lse else None)
     if qk_quant_gran == "per_warp":
-        return per_warp_int8(q, k, km, tensor_layout=tensor_layout, BLKQ=128, WARPQ=warp_q, BLKK=64)
-    return per_thread_int8(q, k, km, tensor_layout=tensor_layout, BLKQ=128, WARPQ=warp_q, BLKK=64, WARPK=64)
+        out = per_warp_int8(q, k, None, tensor_layout=tensor_layout, BLKQ=128, WARPQ=warp_q, BLKK=64)
+    else:
+        out = per_thread_int8(q, k, None, tensor_layout=tensor_layout, BLKQ=128, WARPQ=warp_q, BLKK=64, WARPK=64)
+    return (*out, None)
 
 
 def _launch(fp8, q_int8, k_int8, v, o, q_scale, k_scale, v_scale, v_mean, tensor_layout, is_causal, gran,
@@ -154,9 +159,9 @@ def sageattn_qk_int8_pv_fp16_cuda(
     assert q.stride(-1) == 1 and k.stride(-1) == 1 and v.stride(-1) == 1, "Last dim of qkv must be contiguous."
     if sm_scale is None:
         sm_scale = head_dim_og ** -0.5
-    km, lse_correction = _smooth_k(q, k, tensor_layout, return_lse) if smooth_k else (None, None)
     warp_q = 16 if (q.size(-1) == 128 and pv_accum_dtype == "fp16+fp32") else 32
-    q_int8, q_scale, k_int8, k_scale = _quantize_qk(q, k, km, qk_quant_gran, tensor_layout, warp_q)
+    q_int8, q_scale, k_int8, k_scale, lse_correction = _quantize_qk(q, k, smooth_k, qk_quant_gran, tensor_layout,
+                                                                    warp_q, return_lse)
     o = torch.empty(q.size(), dtype=dtype, device=q.device)
     if pv_accum_dtype in ["fp32", "fp16+fp32"] and smooth_v:
         warnings.warn(f"pv_accum_dtype is {pv_accum_dtype}, smooth_v will be ignored.")
@@ -203,8 +208,8 @@ def sageattn_qk_int8_pv_fp8_cuda(
     assert q.stride(-1) == 1 and k.stride(-1) == 1 and v.stride(-1) == 1, "Last dim of qkv must be contiguous."
     if sm_scale is None:
         sm_scale = head_dim_og ** -0.5
-    km, lse_correction = _smooth_k(q, k, tensor_layout, return_lse) if smooth_k else (None, None)
-    q_int8, q_scale, k_int8, k_scale = _quantize_qk(q, k, km, qk_quant_gran, tensor_layout, 32)
+    q_int8, q_scale, k_int8, k_scale, lse_correction = _quantize_qk(q, k, smooth_k, qk_quant_gran, tensor_layout,
+                                                                    32, return_lse)
     o = torch.empty(q.size(), dtype=dtype, device=q.device)
     if pv_accum_dtype == "fp32+fp32" and smooth_v:
         warnings.warn("pv_accum_dtype is 'fp32+fp32', smooth_v will be ignored.")

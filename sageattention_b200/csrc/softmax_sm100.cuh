@@ -72,8 +72,21 @@ __device__ __forceinline__ void softmax_max(uint32_t (&s)[128], const float (&sc
   for (int k = 0; k < 8; ++k) bias[k] = fmaf(-kMagicF, sc[k], (kFp8 ? kFp8Offset : 0.f) - m_new);
 }
 
+// 2^y for a pair of logits on the FMA pipe (defined below)
+template <int kDeg>
+__device__ __forceinline__ uint64_t exp2_poly2(uint64_t y2);
+__device__ __forceinline__ uint64_t pack2(float lo, float hi);
+__device__ __forceinline__ void unpack2(uint64_t v, float& lo, float& hi);
+
+#ifndef SAGE_POLY_NUM
+#define SAGE_POLY_NUM 0  // of every SAGE_POLY_DEN column pairs, this many take the polynomial
+#endif
+#ifndef SAGE_POLY_DEN
+#define SAGE_POLY_DEN 4
+#endif
+
 // Phase 2: p = 2^(s * sc + bias) in place; returns the row sum of this tile.
-template <bool kMasked>
+template <bool kMasked, int kDeg = 3>
 __device__ __forceinline__ float softmax_exp(uint32_t (&s)[128], const float (&sc)[8],
                                              const float (&bias)[8], int lim) {
   float dsum0 = 0.f, dsum1 = 0.f;
@@ -81,8 +94,15 @@ __device__ __forceinline__ float softmax_exp(uint32_t (&s)[128], const float (&s
   for (int c = 0; c < 128; c += 2) {
     float x0 = __int_as_float((int)s[c] + kMagicI);
     float x1 = __int_as_float((int)s[c + 1] + kMagicI);
-    float p0 = ex2_approx(fmaf(x0, sc[kcls(c)], bias[kcls(c)]));
-    float p1 = ex2_approx(fmaf(x1, sc[kcls(c + 1)], bias[kcls(c + 1)]));
+    float y0 = fmaf(x0, sc[kcls(c)], bias[kcls(c)]);
+    float y1 = fmaf(x1, sc[kcls(c + 1)], bias[kcls(c + 1)]);
+    float p0, p1;
+    if (((c >> 1) % SAGE_POLY_DEN) < SAGE_POLY_NUM) {
+      unpack2(exp2_poly2<kDeg>(pack2(y0, y1)), p0, p1);
+    } else {
+      p0 = ex2_approx(y0);
+      p1 = ex2_approx(y1);
+    }
     if constexpr (kMasked) {
       p0 = (c > lim) ? 0.f : p0;
       p1 = (c + 1 > lim) ? 0.f : p1;

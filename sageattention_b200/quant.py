@@ -143,6 +143,42 @@ def per_thread_int8(q, k, km=None, BLKQ=128, WARPQ=32, BLKK=64, WARPK=64, sm_sca
     return q_int8, q_scale, k_int8, k_scale
 
 
+def smooth_quant_k_int8(k, qk_quant_gran="per_thread", tensor_layout="HND"):
+    """km = k.mean(dim=seq) and the K half of per_warp_int8 / per_thread_int8(…, km) in one launch
+    (the prologue of /root/reference/sageattention/core.py:611-632 for K).  Returns
+    (k_int8, k_scale, km[B,Hkv,D]); codes and scales are those the separate calls give for this km."""
+    _require_cuda(k)
+    lib = _lib.load()
+    b, h, n, d, k4 = _dims(k, tensor_layout)
+    k_int8 = torch.empty(k.shape, dtype=torch.int8, device=k.device)
+    _, _, _, _, ko4 = _dims(k_int8, tensor_layout)
+    per_thread = 1 if qk_quant_gran == "per_thread" else 0
+    per_bh = (n + 63) // 64 * (4 if per_thread else 1)
+    k_scale = torch.empty((b, h, per_bh), dtype=torch.float32, device=k.device)
+    km = torch.empty((b, h, d), dtype=k.dtype, device=k.device)
+    with torch.cuda.device(k.device):
+        _lib.check(lib.sage_smooth_quant_k_int8(k4, km.data_ptr(), ko4, k_scale.data_ptr(), b, h, n, d,
+                                                _dtype_code(k), per_thread, per_bh, _stream(k)))
+    return k_int8, k_scale, km
+
+
+def quant_q_int8(q, qk_quant_gran="per_thread", WARPQ=32, BLKQ=128, tensor_layout="HND"):
+    """The Q half of per_warp_int8 / per_thread_int8 alone."""
+    _require_cuda(q)
+    lib = _lib.load()
+    b, hq, nq, d, q4 = _dims(q, tensor_layout)
+    if qk_quant_gran == "per_warp":
+        return _quant_block(q, None, WARPQ, None, tensor_layout,
+                            scale_per_bh=((nq + BLKQ - 1) // BLKQ) * (BLKQ // WARPQ))
+    q_int8 = torch.empty(q.shape, dtype=torch.int8, device=q.device)
+    _, _, _, _, qo4 = _dims(q_int8, tensor_layout)
+    q_scale = torch.empty((b, hq, (nq + BLKQ - 1) // BLKQ * (BLKQ // WARPQ) * 8), dtype=torch.float32, device=q.device)
+    with torch.cuda.device(q.device):
+        _lib.check(lib.sage_quant_per_thread_int8(q4, None, qo4, q_scale.data_ptr(), b, hq, nq, d, _dtype_code(q),
+                                                  0, WARPQ, _stream(q)))
+    return q_int8, q_scale
+
+
 def sub_mean(v, tensor_layout="HND", vm=None):
     """Reference: /root/reference/sageattention/quant.py:183-223 -> (v_smoothed fp16, vm input dtype).
     `vm` (optional, [B,H,D] in v's dtype) overrides the internally computed mean."""

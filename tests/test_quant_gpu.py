@@ -153,3 +153,23 @@ def test_quantizers_match_cpu_oracle(dtype, layout, n, d, warpq):
             a, bb = mine[i].cpu()[..., :w], orc[i]
             nz = bb != 0
             assert ((a[nz] - bb[nz]).abs() <= bb[nz].abs() * 2.4e-7).all(), f"{name}[{i}] scale beyond 2 ulp"
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("layout", ["HND", "NHD"])
+@pytest.mark.parametrize("gran", ["per_thread", "per_warp"])
+@pytest.mark.parametrize("n,d", [(4096, 128), (1000, 64), (100, 128), (5003, 128), (20000, 64)])
+def test_fused_k_smoothing_equals_separate_calls(dtype, layout, gran, n, d):
+    """sage_smooth_quant_k_int8 (one cluster launch) must give the mean within 1 ulp of torch's and,
+    for ITS mean, exactly the codes and scales of the stand-alone quantiser."""
+    k = make(2, 3, n, d, dtype, layout, 11) + 0.75
+    q = make(2, 3, 128, d, dtype, layout, 12)
+    k_int8, k_scale, km = sb.smooth_quant_k_int8(k, gran, layout)
+    ref = k.mean(dim=2 if layout == "HND" else 1)
+    diff = (km.float() - ref.float()).abs()
+    ulp = ref.float().abs() * (2.0 ** -10 if dtype == torch.float16 else 2.0 ** -7) + 1e-7
+    assert (diff <= ulp).all()
+    fn = sb.per_thread_int8 if gran == "per_thread" else sb.per_warp_int8
+    _, _, k_ref, s_ref = fn(q, k, km, tensor_layout=layout)
+    assert torch.equal(k_int8, k_ref)
+    assert torch.equal(k_scale, s_ref)
