@@ -4,6 +4,7 @@ Exports the same names as /root/reference/sageattention/__init__.py, as real dis
 (the fork aliases them all to one implementation, __init__.py:59-95).
 """
 from .core import sageattn, sageattn_qk_int8_pv_fp16_cuda, sageattn_qk_int8_pv_fp8_cuda
+from .host import HostPipeline
 from .parallel import shard_heads, ulysses_sageattn
 from .quant import (per_block_int8, per_channel_fp8, per_thread_int8, per_warp_int8, quant_q_int8, seq_mean,
                     smooth_quant_k_int8, sub_mean)
@@ -22,6 +23,7 @@ __all__ = [
     "per_thread_int8",
     "sub_mean",
     "per_channel_fp8",
+    "HostPipeline",
     "seq_mean",
     "smooth_quant_k_int8",
     "quant_q_int8",

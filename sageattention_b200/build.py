@@ -24,6 +24,7 @@ UNITS = [
     ("capi.cu", []),
     ("prepass.cu", ["--use_fast_math"]),
     ("attn_sm100.cu", []),
+    ("attn_f16_sm100.cu", []),
 ]
 
 

@@ -1,4 +1,5 @@
-// SageAttention forward for sm_100a (B200): INT8 QK^T + online softmax + FP8/FP16 P.V
+// SageAttention forward for sm_100a (B200), FP8 P.V flavour: INT8 QK^T + online softmax + e4m3 P.V
+// (sage_attn_i8_f8; the f16 P.V entry point lives in attn_f16_sm100.cu)
 //
 // Replaces the reference's mma.sync kernels
 //   qk_int_sv_f16_attn_kernel  (/root/reference/csrc/qattn/qk_int_sv_f16_cuda_sm80.cu:44-671)
@@ -613,11 +614,4 @@ extern "C" int sage_attn_i8_f8(const sage_attn_args* a, void* stream) {
   if (rc) return rc;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   return a->D == 128 ? sage::launch_attn<128, true>(a, s) : sage::launch_attn<64, true>(a, s);
-}
-
-extern "C" int sage_attn_i8_f16(const sage_attn_args* a, void* stream) {
-  int rc = sage::check_attn_args(a);
-  if (rc) return rc;
-  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  return a->D == 128 ? sage::launch_attn<128, false>(a, s) : sage::launch_attn<64, false>(a, s);
 }

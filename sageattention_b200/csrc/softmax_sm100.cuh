@@ -86,12 +86,12 @@ __device__ __forceinline__ void unpack2(uint64_t v, float& lo, float& hi);
 #endif
 
 // Phase 2: p = 2^(s * sc + bias) in place; returns the row sum of this tile.
-template <bool kMasked, int kDeg = 3>
+template <bool kMasked, int kLo = 0, int kHi = 128, int kDeg = 3>
 __device__ __forceinline__ float softmax_exp(uint32_t (&s)[128], const float (&sc)[8],
                                              const float (&bias)[8], int lim) {
   float dsum0 = 0.f, dsum1 = 0.f;
 #pragma unroll
-  for (int c = 0; c < 128; c += 2) {
+  for (int c = kLo; c < kHi; c += 2) {
     float x0 = __int_as_float((int)s[c] + kMagicI);
     float x1 = __int_as_float((int)s[c + 1] + kMagicI);
     float y0 = fmaf(x0, sc[kcls(c)], bias[kcls(c)]);

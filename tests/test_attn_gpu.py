@@ -190,3 +190,22 @@ def test_errors_match_reference_conventions():
     # SDPA-style extra kwargs are swallowed (modify_wan.py:70-72)
     o = sb.sageattn(q, k, v, attn_mask=None, dropout_p=0.0)
     assert o.shape == q.shape
+
+
+def test_host_pipeline_matches_direct_calls():
+    """HostPipeline (pinned host q/k/v -> three-stream pipeline) returns what the operator returns
+    for device copies of the same inputs, for every queued step."""
+    from sageattention_b200 import HostPipeline
+    torch.manual_seed(3)
+    shape = (1, 4, 1024, 128)
+    steps = 5
+    hq, hk, hv = ([torch.randn(shape, dtype=torch.float16).pin_memory() for _ in range(steps)] for _ in range(3))
+    outs = [torch.empty(shape, dtype=torch.float16).pin_memory() for _ in range(steps)]
+    pipe = HostPipeline(sb.sageattn_qk_int8_pv_fp16_cuda, shape, torch.float16)
+    for i in range(steps):
+        pipe.submit(hq[i], hk[i], hv[i], outs[i], is_causal=bool(i & 1))
+    pipe.drain()
+    torch.cuda.synchronize()
+    for i in range(steps):
+        ref = sb.sageattn_qk_int8_pv_fp16_cuda(hq[i].cuda(), hk[i].cuda(), hv[i].cuda(), is_causal=bool(i & 1))
+        assert torch.equal(outs[i], ref.cpu()), f"step {i}"

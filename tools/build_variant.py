@@ -14,7 +14,12 @@ try:
     subprocess.check_call([B._nvcc(), "-c", tmp, "-o", obj] + B.ARCH + B.COMMON + sys.argv[3:])
 finally:
     os.remove(tmp)
-objs = [os.path.join(B.OBJ, n + ".o") for n, _ in B.UNITS if n != "attn_sm100.cu"] + [obj]
+# the variant replaces the unit(s) whose entry points it defines (older experiments define both)
+text = open(src).read()
+drop = {"attn_sm100.cu"} if 'int sage_attn_i8_f8(' in text else set()
+if 'int sage_attn_i8_f16(' in text:
+    drop.add("attn_f16_sm100.cu")
+objs = [os.path.join(B.OBJ, n + ".o") for n, _ in B.UNITS if n not in drop] + [obj]
 lib = os.path.join(out, f"libsage_{name}.so")
 subprocess.check_call([B._nvcc(), "-shared", "-o", lib] + objs + B.ARCH)
 print(lib)
