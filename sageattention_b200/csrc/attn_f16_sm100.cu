@@ -42,6 +42,11 @@ __device__ long long g_trace[3][kTraceSteps][kTraceSlots];
 #define SAGE_STAMP(who, j, slot) do { } while (0)
 #endif
 
+// 0 = the two softmax warpgroups run freely, 2 = whole softmax steps alternate (see attn_sm100.cu)
+#ifndef SAGE_TURN
+#define SAGE_TURN 0
+#endif
+
 constexpr int kTileQ = 128;       // rows per Q tile (= TMEM lanes)
 constexpr int kTileKV = 128;      // kv rows per step
 constexpr int kKStages = 2;
@@ -88,7 +93,7 @@ template <int D, bool kFp8>
 __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int t, int row,
                                                   int q_tile_start, int n_iter, int b, int h,
                                                   int hkv, uint32_t tmem_base, uint64_t* s_full,
-                                                  uint64_t* p_full, uint64_t* o_full) {
+                                                  uint64_t* p_full, uint64_t* o_full, int n_pp) {
   const int warp_in_wg = (row >> 5);
   const uint32_t lane_off = (uint32_t)(warp_in_wg * 32) << 16;
   const uint32_t tS = tmem_base + lane_off + (uint32_t)(t * 128);
@@ -108,6 +113,7 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
   const float* ksp = p.k_scale + (size_t)(b * p.Hkv + hkv) * p.k_scale_per_bh;
 
   float m_run = -1e30f, d_run = 0.f;
+  if (SAGE_TURN == 2 && t == 1 && n_pp > 0) named_bar_arrive(1, 2 * kTileQ);
 #ifdef SAGE_TRACE
   const bool trace_on = (blockIdx.x | blockIdx.y | blockIdx.z) == 0 && row == 0;
 #endif
@@ -126,6 +132,7 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
     }
     SAGE_STAMP(t, j, 0);
     mbar_wait(&s_full[t], j & 1);
+    if (SAGE_TURN == 2 && j < n_pp) named_bar_sync(1 + t, 2 * kTileQ);
     tc_fence_after();
     SAGE_STAMP(t, j, 1);
     uint32_t s[128];
@@ -182,6 +189,7 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
     tc_wait_st();
     tc_fence_before();
     mbar_arrive(&p_full[t]);
+    if (SAGE_TURN == 2 && j < n_pp - t) named_bar_arrive(2 - t, 2 * kTileQ);
     SAGE_STAMP(t, j, 4);
   }
 
@@ -302,7 +310,7 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     const int row = threadIdx.x & 127;
     if (n_it[t] > 0)
       softmax_warpgroup<D, kFp8>(p, t, row, q_start + t * kTileQ, n_it[t], b, h, hkv, tmem_base,
-                                 s_full, p_full, o_full);
+                                 s_full, p_full, o_full, min(n_it[0], n_it[1]));
   } else if (warp == 8) {
     // ======================= TMA producer =======================
     reg_dealloc<kIssueRegs>();

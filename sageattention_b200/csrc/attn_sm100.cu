@@ -54,6 +54,12 @@ __device__ long long g_trace[3][kTraceSteps][kTraceSlots];
 #define SAGE_STAMP(who, j, slot) do { } while (0)
 #endif
 
+// How the two softmax warpgroups take turns: 1 = only their exp phases alternate, 2 = whole softmax
+// steps alternate (a warpgroup computes alone on its schedulers while the other one's MMAs run).
+#ifndef SAGE_TURN
+#define SAGE_TURN 1
+#endif
+
 constexpr int kTileQ = 128;       // rows per Q tile (= TMEM lanes)
 constexpr int kTileKV = 128;      // kv rows per step
 constexpr int kKStages = 2;
@@ -129,7 +135,7 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
   // named barrier 1: "warpgroup 0 may start exp" (first pass granted here by warpgroup 1),
   // named barrier 2: "warpgroup 1 may start exp".  Only the first n_pingpong steps, which both
   // warpgroups execute, take part.
-  if (t == 1 && n_pingpong > 0) named_bar_arrive(1, 2 * kTileQ);
+  if (SAGE_TURN != 0 && t == 1 && n_pingpong > 0) named_bar_arrive(1, 2 * kTileQ);
 #ifdef SAGE_TRACE
   const bool trace_on = (blockIdx.x | blockIdx.y | blockIdx.z) == 0 && row == 0;
 #endif
@@ -148,6 +154,7 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
     }
     SAGE_STAMP(t, j, 0);
     mbar_wait(&s_full[t], j & 1);
+    if (SAGE_TURN == 2 && j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
     tc_fence_after();
     SAGE_STAMP(t, j, 1);
     uint32_t s[128];
@@ -183,11 +190,11 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
     // The exp phases of the two warpgroups alternate (they are the only MUFU-bound stretch): each
     // warpgroup's load / max / pack / store phases then run under the other one's exponentials.
     SAGE_STAMP(t, j, 5);
-    if (j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
+    if (SAGE_TURN == 1 && j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
     SAGE_STAMP(t, j, 6);
     if (masked_tile) dsum = softmax_exp<true>(s, sc, bias, lim);
     else dsum = softmax_exp<false>(s, sc, bias, 127);
-    if (j < n_pingpong - t) named_bar_arrive(2 - t, 2 * kTileQ);
+    if (SAGE_TURN == 1 && j < n_pingpong - t) named_bar_arrive(2 - t, 2 * kTileQ);
     SAGE_STAMP(t, j, 7);
     d_run = fmaf(d_run, alpha, dsum);
     softmax_pack<kFp8>(s, w);
@@ -223,6 +230,7 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
     }
     fence_proxy_async_smem();
     mbar_arrive(&p_full[t]);
+    if (SAGE_TURN == 2 && j < n_pingpong - t) named_bar_arrive(2 - t, 2 * kTileQ);
     SAGE_STAMP(t, j, 4);
   }
 
