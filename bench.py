@@ -105,10 +105,14 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, pw, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for ts, ln in self.lines:
-            # only samples taken inside the timed region count
-            if t_begin is not None and not (t_begin <= ts <= t_end):
-                continue
+        # only samples taken inside the timed region count; a region shorter than the 50 ms sampling
+        # period falls back to the samples within 100 ms of it
+        lines = self.lines
+        if t_begin is not None:
+            lines = [(ts, ln) for ts, ln in self.lines if t_begin <= ts <= t_end]
+            if not lines:
+                lines = [(ts, ln) for ts, ln in self.lines if t_begin - 0.1 <= ts <= t_end + 0.1]
+        for ts, ln in lines:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 7:
                 continue

@@ -17,6 +17,8 @@
  *   sage_attn_i8_f16             <- _qattn_sm80.qk_int8_sv_f16_accum_{f32,f16,f16_inst_buf}_attn,
  *                                   ..._fuse_v_mean_attn (csrc/qattn/pybind_sm80.cpp, qk_int_sv_f16_cuda_sm80.cu:674-1379)
  *   sage_attn_i8_f8              <- _qattn_sm89.qk_int8_sv_f8_accum_* (7 variants, csrc/qattn/pybind_sm89.cpp)
+ *   sage_prepass_qk_int8         <- the whole Q/K prologue of the operator with smooth_k (sageattention/core.py:611-632,
+ *                                   794-812: k.mean, per_warp_int8 / per_thread_int8 for q and k) in one launch
  *   sage_smooth_quant_k_int8     <- `km = k.mean(dim=seq)` followed by the K half of per_warp_int8 /
  *                                   per_thread_int8 (sageattention/core.py:611-632), fused in one launch
  */
@@ -81,6 +83,16 @@ int sage_quant_per_thread_int8(sage_tensor4 x, const void* mean, sage_tensor4 ou
  * scale: [B,H,scale_per_bh], scale_per_bh >= ceil(N/64) (per_thread = 0) or ceil(N/64)*4. */
 int sage_smooth_quant_k_int8(sage_tensor4 k, void* mean_out, sage_tensor4 out, float* scale, int B, int H,
                              int N, int D, int dtype, int per_thread, int scale_per_bh, void* stream);
+
+/* The Q/K prologue in one launch: what sage_smooth_quant_k_int8(k) and the Q half
+ * (sage_quant_per_thread_int8(is_key = 0, tile = warp_q) if per_thread, else sage_quant_int8(block =
+ * warp_q)) produce, bit for bit.  q: [B,Hq,Nq,D], k: [B,Hkv,Nk,D] (strides given); k_mean_out [B,Hkv,D].
+ * q_scale: [B,Hq,q_scale_per_bh] (>= ceil(Nq/128)*(128/warp_q)*8 per_thread, >= ceil(Nq/warp_q) else),
+ * k_scale: [B,Hkv,k_scale_per_bh] (>= ceil(Nk/64)*4 per_thread, >= ceil(Nk/64) else). */
+int sage_prepass_qk_int8(sage_tensor4 q, sage_tensor4 k, sage_tensor4 q_out, sage_tensor4 k_out,
+                         float* q_scale, float* k_scale, void* k_mean_out, int B, int Hq, int Hkv, int Nq,
+                         int Nk, int D, int dtype, int per_thread, int warp_q, int q_scale_per_bh,
+                         int k_scale_per_bh, void* stream);
 
 /* out(f16)[b,h,n,d] = half( x - mean ) in the input type's packed arithmetic. */
 int sage_sub_mean(sage_tensor4 x, const void* mean, sage_tensor4 out, int B, int H, int N, int D,

@@ -44,6 +44,7 @@ SIGNATURES = {
                                            c_int, c_int, c_vp]),
     "sage_smooth_quant_k_int8": (c_int, [Tensor4, c_vp, Tensor4, c_vp, c_int, c_int, c_int, c_int, c_int,
                                          c_int, c_int, c_vp]),
+    "sage_prepass_qk_int8": (c_int, [Tensor4, Tensor4, Tensor4, Tensor4, c_vp, c_vp, c_vp] + [c_int] * 11 + [c_vp]),
     "sage_sub_mean": (c_int, [Tensor4, c_vp, Tensor4, c_int, c_int, c_int, c_int, c_int, c_vp]),
     "sage_per_channel_fp8_workspace_bytes": (ctypes.c_size_t, [c_int] * 4),
     "sage_per_channel_fp8": (c_int, [Tensor4, c_vp, c_i64, c_i64, c_i64, c_vp, c_vp, c_int, c_int, c_int,
@@ -58,7 +59,7 @@ _lib = None
 # bumped on every call so bench.py can report how many of OUR kernels ran in its timed region.
 KERNELS_PER_CALL = {
     "sage_seq_mean": 1, "sage_quant_int8": 1, "sage_quant_per_thread_int8": 1, "sage_sub_mean": 1,
-    "sage_smooth_quant_k_int8": 1,
+    "sage_smooth_quant_k_int8": 1, "sage_prepass_qk_int8": 1,
     "sage_per_channel_fp8": 2, "sage_attn_i8_f16": 1, "sage_attn_i8_f8": 1,
 }
 LAUNCHES = 0

@@ -162,6 +162,33 @@ def smooth_quant_k_int8(k, qk_quant_gran="per_thread", tensor_layout="HND"):
     return k_int8, k_scale, km
 
 
+def prepass_qk_int8(q, k, qk_quant_gran="per_thread", WARPQ=32, tensor_layout="HND"):
+    """The operator's Q/K prologue with smooth_k in ONE launch (core.py:611-632): km = k.mean(seq),
+    K codes/scales for that mean and Q codes/scales.  Returns (q_int8, q_scale, k_int8, k_scale, km),
+    identical to quant_q_int8(q) + smooth_quant_k_int8(k)."""
+    _require_cuda(q, k)
+    lib = _lib.load()
+    b, hq, nq, d, q4 = _dims(q, tensor_layout)
+    _, hk, nk, _, k4 = _dims(k, tensor_layout)
+    per_thread = 1 if qk_quant_gran == "per_thread" else 0
+    q_int8 = torch.empty(q.shape, dtype=torch.int8, device=q.device)
+    k_int8 = torch.empty(k.shape, dtype=torch.int8, device=k.device)
+    _, _, _, _, qo4 = _dims(q_int8, tensor_layout)
+    _, _, _, _, ko4 = _dims(k_int8, tensor_layout)
+    q_per_bh = (nq + 127) // 128 * (128 // WARPQ) * (8 if per_thread else 1)
+    k_per_bh = (nk + 63) // 64 * (4 if per_thread else 1)
+    # per_warp: entries past ceil(Nq/WARPQ) are never written by the reference either (torch.empty there)
+    q_scale = (torch.empty if per_thread or q_per_bh == (nq + WARPQ - 1) // WARPQ else torch.zeros)(
+        (b, hq, q_per_bh), dtype=torch.float32, device=q.device)
+    k_scale = torch.empty((b, hk, k_per_bh), dtype=torch.float32, device=q.device)
+    km = torch.empty((b, hk, d), dtype=k.dtype, device=k.device)
+    with torch.cuda.device(q.device):
+        _lib.check(lib.sage_prepass_qk_int8(q4, k4, qo4, ko4, q_scale.data_ptr(), k_scale.data_ptr(), km.data_ptr(),
+                                            b, hq, hk, nq, nk, d, _dtype_code(q), per_thread, WARPQ, q_per_bh,
+                                            k_per_bh, _stream(q)))
+    return q_int8, q_scale, k_int8, k_scale, km
+
+
 def quant_q_int8(q, qk_quant_gran="per_thread", WARPQ=32, BLKQ=128, tensor_layout="HND"):
     """The Q half of per_warp_int8 / per_thread_int8 alone."""
     _require_cuda(q)

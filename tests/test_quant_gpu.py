@@ -173,3 +173,23 @@ def test_fused_k_smoothing_equals_separate_calls(dtype, layout, gran, n, d):
     _, _, k_ref, s_ref = fn(q, k, km, tensor_layout=layout)
     assert torch.equal(k_int8, k_ref)
     assert torch.equal(k_scale, s_ref)
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("layout", ["HND", "NHD"])
+@pytest.mark.parametrize("gran,warpq", [("per_thread", 32), ("per_thread", 16), ("per_warp", 32), ("per_warp", 16)])
+@pytest.mark.parametrize("nq,nk,d,hq,hk", [(4096, 4096, 128, 4, 4), (1000, 1500, 64, 4, 2), (77, 100, 128, 2, 2),
+                                           (130, 5003, 128, 6, 2)])
+def test_single_launch_qk_prologue_equals_separate_calls(dtype, layout, gran, warpq, nq, nk, d, hq, hk):
+    """sage_prepass_qk_int8 (Q tiles and K clusters in one grid) = quant_q_int8 + smooth_quant_k_int8, bit for bit
+    (GQA head counts and different q / kv lengths included)."""
+    q = make(2, hq, nq, d, dtype, layout, 21)
+    k = make(2, hk, nk, d, dtype, layout, 22) + 0.5
+    q8, qs, k8, ks, km = sb.prepass_qk_int8(q, k, gran, WARPQ=warpq, tensor_layout=layout)
+    q8r, qsr = sb.quant_q_int8(q, gran, WARPQ=warpq, tensor_layout=layout)
+    k8r, ksr, kmr = sb.smooth_quant_k_int8(k, gran, layout)
+    assert torch.equal(km, kmr)
+    assert torch.equal(k8, k8r) and torch.equal(ks, ksr)
+    assert torch.equal(q8, q8r)
+    nwritten = (nq + warpq - 1) // warpq if gran == "per_warp" else qs.size(-1)
+    assert torch.equal(qs[..., :nwritten], qsr[..., :nwritten])
