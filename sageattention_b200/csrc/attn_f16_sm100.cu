@@ -47,6 +47,12 @@ __device__ long long g_trace[3][kTraceSteps][kTraceSlots];
 #define SAGE_TURN 0
 #endif
 
+// Development aid: warpgroup 1 starts its first step this many SM cycles late (phase offset
+// between the two softmax warpgroups without any per-step barrier).
+#ifndef SAGE_DELAY
+#define SAGE_DELAY 0
+#endif
+
 constexpr int kTileQ = 128;       // rows per Q tile (= TMEM lanes)
 constexpr int kTileKV = 128;      // kv rows per step
 constexpr int kKStages = 2;
@@ -118,6 +124,10 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
   const bool trace_on = (blockIdx.x | blockIdx.y | blockIdx.z) == 0 && row == 0;
 #endif
 
+  if (SAGE_DELAY > 0 && t == 1) {
+    const long long t_go = clock64() + SAGE_DELAY;
+    while (clock64() < t_go) __nanosleep(100);
+  }
   for (int j = 0; j < n_iter; ++j) {
     // k scales of this tile -> 8 class scales
     float sc[8];

@@ -60,6 +60,12 @@ __device__ long long g_trace[3][kTraceSteps][kTraceSlots];
 #define SAGE_TURN 1
 #endif
 
+// Development aid: warpgroup 1 starts its first step this many SM cycles late (phase offset
+// between the two softmax warpgroups without any per-step barrier).
+#ifndef SAGE_DELAY
+#define SAGE_DELAY 0
+#endif
+
 constexpr int kTileQ = 128;       // rows per Q tile (= TMEM lanes)
 constexpr int kTileKV = 128;      // kv rows per step
 constexpr int kKStages = 2;
@@ -140,6 +146,10 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
   const bool trace_on = (blockIdx.x | blockIdx.y | blockIdx.z) == 0 && row == 0;
 #endif
 
+  if (SAGE_DELAY > 0 && t == 1) {
+    const long long t_go = clock64() + SAGE_DELAY;
+    while (clock64() < t_go) __nanosleep(100);
+  }
   for (int j = 0; j < n_iter; ++j) {
     // k scales of this tile -> 8 class scales
     float sc[8];
@@ -187,39 +197,30 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
     uint32_t w[kFp8 ? 32 : 64];
     if (masked_tile) softmax_max<kFp8, true>(s, sc, lim, m_run, alpha, bias);
     else softmax_max<kFp8, false>(s, sc, 127, m_run, alpha, bias);
-    // The exp phases of the two warpgroups alternate (they are the only MUFU-bound stretch): each
-    // warpgroup's load / max / pack / store phases then run under the other one's exponentials.
     SAGE_STAMP(t, j, 5);
-    if (SAGE_TURN == 1 && j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
-    SAGE_STAMP(t, j, 6);
-    if (masked_tile) dsum = softmax_exp<true>(s, sc, bias, lim);
-    else dsum = softmax_exp<false>(s, sc, bias, 127);
-    if (SAGE_TURN == 1 && j < n_pingpong - t) named_bar_arrive(2 - t, 2 * kTileQ);
-    SAGE_STAMP(t, j, 7);
-    d_run = fmaf(d_run, alpha, dsum);
-    softmax_pack<kFp8>(s, w);
-    SAGE_STAMP(t, j, 3);
-    // PV(j-1) complete: P tile reusable and O_t stable
-    if (j > 0) {
-      mbar_wait(&p_empty[t], (j - 1) & 1);
-      // rescale O when some row of this warp moved its max
-      if (__any_sync(0xffffffffu, alpha != 1.0f)) {
-        tc_fence_after();
+    auto rescale_o = [&]() {
+      // PV(j-1) complete: P tile reusable and O_t stable
+      if (j > 0) {
+        mbar_wait(&p_empty[t], (j - 1) & 1);
+        // rescale O when some row of this warp moved its max
+        if (__any_sync(0xffffffffu, alpha != 1.0f)) {
+          tc_fence_after();
 #pragma unroll
-        for (int c0 = 0; c0 < D; c0 += 32) {
-          uint32_t o[32];
-          tmem_ld32(tO + c0, o);
-          tc_wait_ld();
+          for (int c0 = 0; c0 < D; c0 += 32) {
+            uint32_t o[32];
+            tmem_ld32(tO + c0, o);
+            tc_wait_ld();
 #pragma unroll
-          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-          tmem_st32(tO + c0, o);
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st32(tO + c0, o);
+          }
+          tc_wait_st();
+          tc_fence_before();
         }
-        tc_wait_st();
-        tc_fence_before();
       }
-    }
-    // P row -> smem, K-major 128B-swizzled (16B chunk c of row r sits at chunk c ^ (r & 7))
-    {
+    };
+    auto store_p = [&]() {
+      // P row -> smem, K-major 128B-swizzled (16B chunk c of row r sits at chunk c ^ (r & 7))
       const uint32_t prow = smem_u32(p_smem) + (uint32_t)row * 128u;
       const uint32_t x = (uint32_t)(row & 7);
 #pragma unroll
@@ -227,6 +228,37 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
         const uint32_t addr = prow + (uint32_t)(c >> 3) * (kTileQ * 128) + (((uint32_t)(c & 7) ^ x) << 4);
         st_shared_v4(addr, w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
       }
+    };
+    if (SAGE_TURN == 3) {
+      // The MUFU-bound stretch of the two warpgroups alternates, and it is ONE straight-line block:
+      // exponentials, row sum, packing and the smem stores, so that the conversions and stores of
+      // finished columns fill the issue slots the MUFU cadence leaves (the O-rescale check, which
+      // only needs alpha, moves in front of it).
+      rescale_o();
+      if (j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
+      SAGE_STAMP(t, j, 6);
+      if (masked_tile) dsum = softmax_exp<true>(s, sc, bias, lim);
+      else dsum = softmax_exp<false>(s, sc, bias, 127);
+      d_run = fmaf(d_run, alpha, dsum);
+      softmax_pack<kFp8>(s, w);
+      store_p();
+      if (j < n_pingpong - t) named_bar_arrive(2 - t, 2 * kTileQ);
+      SAGE_STAMP(t, j, 7);
+      SAGE_STAMP(t, j, 3);
+    } else {
+      // The exp phases of the two warpgroups alternate (they are the only MUFU-bound stretch): each
+      // warpgroup's load / max / pack / store phases then run under the other one's exponentials.
+      if (SAGE_TURN == 1 && j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
+      SAGE_STAMP(t, j, 6);
+      if (masked_tile) dsum = softmax_exp<true>(s, sc, bias, lim);
+      else dsum = softmax_exp<false>(s, sc, bias, 127);
+      if (SAGE_TURN == 1 && j < n_pingpong - t) named_bar_arrive(2 - t, 2 * kTileQ);
+      SAGE_STAMP(t, j, 7);
+      d_run = fmaf(d_run, alpha, dsum);
+      softmax_pack<kFp8>(s, w);
+      SAGE_STAMP(t, j, 3);
+      rescale_o();
+      store_p();
     }
     fence_proxy_async_smem();
     mbar_arrive(&p_full[t]);
