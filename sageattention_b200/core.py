@@ -63,15 +63,11 @@ def _quantize_qk(q, k, smooth_k, qk_quant_gran, tensor_layout, warp_q, return_ls
     mean + quantise launch (smooth_k) or the plain quantiser.  Returns the four quantiser outputs
     and the LSE correction (None unless smooth_k and return_lse)."""
     if smooth_k:
-        if qk_quant_gran == "per_warp":
-            # one launch for the whole prologue (measured at C2: 99 us against 45 + 66 us)
-            q_int8, q_scale, k_int8, k_scale, km = prepass_qk_int8(q, k, qk_quant_gran, WARPQ=warp_q,
-                                                                     tensor_layout=tensor_layout)
-        else:
-            # per_thread tiles are ALU-heavier and lose in the cluster-launched mixed grid
-            # (170 us against 56 + 88 us): Q tiles and the cluster-fused K launch stay separate
-            q_int8, q_scale = quant_q_int8(q, qk_quant_gran, WARPQ=warp_q, BLKQ=128, tensor_layout=tensor_layout)
-            k_int8, k_scale, km = smooth_quant_k_int8(k, qk_quant_gran, tensor_layout)
+        # one cluster-launched grid for the whole prologue: K slices (mean + quantise, K read once
+        # from HBM) and Q tiles side by side (measured at C2: per_thread 105 us against 41 + 72 us as
+        # two launches, per_warp 89 us against 45 + 62 us)
+        q_int8, q_scale, k_int8, k_scale, km = prepass_qk_int8(q, k, qk_quant_gran, WARPQ=warp_q,
+                                                                 tensor_layout=tensor_layout)
         return q_int8, q_scale, k_int8, k_scale, (_lse_correction(q, km, tensor_layout) if return_lse else None)
     if qk_quant_gran == "per_warp":
         out = per_warp_int8(q, k, None, tensor_layout=tensor_layout, BLKQ=128, WARPQ=warp_q, BLKK=64)
