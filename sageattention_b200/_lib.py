@@ -60,7 +60,9 @@ _lib = None
 KERNELS_PER_CALL = {
     "sage_seq_mean": 1, "sage_quant_int8": 1, "sage_quant_per_thread_int8": 1, "sage_sub_mean": 1,
     "sage_smooth_quant_k_int8": 1, "sage_prepass_qk_int8": 1,
-    "sage_per_channel_fp8": 2, "sage_attn_i8_f16": 1, "sage_attn_i8_f8": 1,
+    # smooth_v: statistics + conversion; otherwise one cluster launch
+    "sage_per_channel_fp8": (lambda a: 2 if a[14] else 1),
+    "sage_attn_i8_f16": 1, "sage_attn_i8_f8": 1,
 }
 LAUNCHES = 0
 
@@ -73,7 +75,7 @@ class _Counted:
 
     def __call__(self, *a):
         global LAUNCHES
-        LAUNCHES += self._n
+        LAUNCHES += self._n(a) if callable(self._n) else self._n
         return self._fn(*a)
 
 
