@@ -66,6 +66,13 @@ __device__ long long g_trace[3][kTraceSteps][kTraceSlots];
 #define SAGE_DELAY 0
 #endif
 
+// 1 (measured slower, 14.4 vs 13.4 ms, default 0): the softmax warpgroups pre-set S_t in TMEM to the magic constant 0x4B400000 before every QK MMA
+// (which then always accumulates), so the logits come out of tcgen05.ld as the bits of the float
+// 1.5*2^23 + S: 8 tcgen05.st per thread and step replace 128 integer adds.
+#ifndef SAGE_BIAS_S
+#define SAGE_BIAS_S 0
+#endif
+
 constexpr int kTileQ = 128;       // rows per Q tile (= TMEM lanes)
 constexpr int kTileKV = 128;      // kv rows per step
 constexpr int kKStages = 2;
@@ -138,6 +145,23 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
   const float* ksp = p.k_scale + (size_t)(b * p.Hkv + hkv) * p.k_scale_per_bh;
 
   float m_run = -1e30f, d_run = 0.f;
+  constexpr bool kBiased = SAGE_BIAS_S != 0;
+  auto preset_s = [&]() {
+    if constexpr (kBiased) {
+      uint32_t mg[16];
+#pragma unroll
+      for (int i = 0; i < 16; ++i) mg[i] = (uint32_t)kMagicI;
+#pragma unroll
+      for (int c0 = 0; c0 < 128; c0 += 16) tmem_st16(tS + c0, mg);
+      tc_wait_st();
+    }
+  };
+  if constexpr (kBiased) {
+    // S_t(0) accumulates onto the constant as well: phase 0 of s_free is "preset done"
+    preset_s();
+    tc_fence_before();
+    mbar_arrive(&s_free[t]);
+  }
   // named barrier 1: "warpgroup 0 may start exp" (first pass granted here by warpgroup 1),
   // named barrier 2: "warpgroup 1 may start exp".  Only the first n_pingpong steps, which both
   // warpgroups execute, take part.
@@ -180,6 +204,7 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
       tc_wait_ld();
     }
     // S_t is in registers: the issuer may overwrite it with S_t(j+1)
+    preset_s();
     tc_fence_before();
     mbar_arrive(&s_free[t]);
     SAGE_STAMP(t, j, 2);
@@ -187,7 +212,7 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
       const int nq_pad = (p.Nq + 255) / 256 * 256;
       int* dst = p.debug_s + ((size_t)(b * p.Hq + h) * nq_pad + q_row) * 128;
 #pragma unroll
-      for (int c = 0; c < 128; ++c) dst[c] = (int)s[c];
+      for (int c = 0; c < 128; ++c) dst[c] = (int)s[c] - (kBiased ? kMagicI : 0);
     }
     const int kv0 = j * kTileKV;
     int lim = p.Nk - 1 - kv0;
@@ -195,8 +220,8 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
     const bool masked_tile = (j == n_iter - 1) && (p.causal || (p.Nk - kv0) < kTileKV);
     float alpha, bias[8], dsum;
     uint32_t w[kFp8 ? 32 : 64];
-    if (masked_tile) softmax_max<kFp8, true>(s, sc, lim, m_run, alpha, bias);
-    else softmax_max<kFp8, false>(s, sc, 127, m_run, alpha, bias);
+    if (masked_tile) softmax_max<kFp8, true, kBiased>(s, sc, lim, m_run, alpha, bias);
+    else softmax_max<kFp8, false, kBiased>(s, sc, 127, m_run, alpha, bias);
     SAGE_STAMP(t, j, 5);
     auto rescale_o = [&]() {
       // PV(j-1) complete: P tile reusable and O_t stable
@@ -237,8 +262,8 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
       rescale_o();
       if (j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
       SAGE_STAMP(t, j, 6);
-      if (masked_tile) dsum = softmax_exp<true>(s, sc, bias, lim);
-      else dsum = softmax_exp<false>(s, sc, bias, 127);
+      if (masked_tile) dsum = softmax_exp<true, 0, 128, 3, kBiased>(s, sc, bias, lim);
+      else dsum = softmax_exp<false, 0, 128, 3, kBiased>(s, sc, bias, 127);
       d_run = fmaf(d_run, alpha, dsum);
       softmax_pack<kFp8>(s, w);
       store_p();
@@ -250,8 +275,8 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
       // warpgroup's load / max / pack / store phases then run under the other one's exponentials.
       if (SAGE_TURN == 1 && j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
       SAGE_STAMP(t, j, 6);
-      if (masked_tile) dsum = softmax_exp<true>(s, sc, bias, lim);
-      else dsum = softmax_exp<false>(s, sc, bias, 127);
+      if (masked_tile) dsum = softmax_exp<true, 0, 128, 3, kBiased>(s, sc, bias, lim);
+      else dsum = softmax_exp<false, 0, 128, 3, kBiased>(s, sc, bias, 127);
       if (SAGE_TURN == 1 && j < n_pingpong - t) named_bar_arrive(2 - t, 2 * kTileQ);
       SAGE_STAMP(t, j, 7);
       d_run = fmaf(d_run, alpha, dsum);
@@ -437,7 +462,7 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         for (int kk = 0; kk < D / 32; ++kk) {
           const uint64_t ad = make_smem_desc(a0 + kk * 32, 16, qk_sbo, qk_swz);
           const uint64_t bd = make_smem_desc(b0 + kk * 32, 16, qk_sbo, qk_swz);
-          mma_i8_ss(tmem_base + t * 128, ad, bd, idesc_qk, kk > 0);
+          mma_i8_ss(tmem_base + t * 128, ad, bd, idesc_qk, (SAGE_BIAS_S != 0) || kk > 0);
         }
       };
       const uint32_t sP = smem_u32(smem + L::kPOff);
@@ -471,7 +496,14 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       mbar_wait(&k_full[0], 0);
       tc_fence_after();
       for (int t = 0; t < 2; ++t)
-        if (n_it[t] > 0) { issue_qk(t, 0); tc_commit(&s_full[t]); }
+        if (n_it[t] > 0) {
+          if (SAGE_BIAS_S != 0) {  // S_t has been pre-set by its warpgroup
+            mbar_wait(&s_free[t], 0);
+            tc_fence_after();
+          }
+          issue_qk(t, 0);
+          tc_commit(&s_full[t]);
+        }
       tc_commit(&k_empty[0]);
 
       for (int j = 0; j < n_max; ++j) {
@@ -482,7 +514,7 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
           for (int t = 0; t < 2; ++t) {
             if (j + 1 < n_it[t]) {
               SAGE_STAMP(2, j, t * 4 + 0);
-              mbar_wait(&s_free[t], j & 1);
+              mbar_wait(&s_free[t], (j + (SAGE_BIAS_S != 0 ? 1 : 0)) & 1);
               tc_fence_after();
               SAGE_STAMP(2, j, t * 4 + 1);
               issue_qk(t, j + 1);

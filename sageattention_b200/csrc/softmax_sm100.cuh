@@ -19,11 +19,16 @@ constexpr int kMaskedS = -4194304;  // below any reachable int8 dot product (|S|
 __device__ __forceinline__ constexpr int kcls(int c) { return (c >> 6) * 4 + ((c & 7) >> 1); }
 
 __device__ __forceinline__ uint32_t pack_e4m3x4(float a0, float a1, float a2, float a3) {
-  // byte0 = a0, byte1 = a1, byte2 = a2, byte3 = a3
-  uint16_t lo, hi;
-  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;\n" : "=h"(lo) : "f"(a1), "f"(a0));
-  asm("cvt.rn.satfinite.e4m3x2.f32 %0, %1, %2;\n" : "=h"(hi) : "f"(a3), "f"(a2));
-  return (uint32_t)lo | ((uint32_t)hi << 16);
+  // byte0 = a0, byte1 = a1, byte2 = a2, byte3 = a3.  The two halves are joined with a vector mov so
+  // that ptxas uses F2FP's merge form (two instructions, no PRMT).
+  uint32_t r;
+  asm("{ .reg .b16 lo, hi;\n"
+      "  cvt.rn.satfinite.e4m3x2.f32 lo, %2, %1;\n"
+      "  cvt.rn.satfinite.e4m3x2.f32 hi, %4, %3;\n"
+      "  mov.b32 %0, {lo, hi}; }\n"
+      : "=r"(r)
+      : "f"(a0), "f"(a1), "f"(a2), "f"(a3));
+  return r;
 }
 __device__ __forceinline__ uint32_t pack_f16x2(float a0, float a1) {
   uint32_t r;
@@ -38,26 +43,29 @@ __device__ __forceinline__ uint32_t pack_f16x2(float a0, float a1) {
 
 // Phase 1: (masking,) row max, lazy-rescale decision.  Out: m_run updated, alpha (1 when the
 // accumulators keep their scale), bias[] for phase 2.
-template <bool kFp8, bool kMasked>
+// kBiased: the logits arrive as S + kMagicI (the accumulator was pre-set to the magic constant, so
+// the bits ARE the float 1.5*2^23 + S and no per-element int->float add is needed).
+template <bool kFp8, bool kMasked, bool kBiased = false>
 __device__ __forceinline__ void softmax_max(uint32_t (&s)[128], const float (&sc)[8], int lim,
                                             float& m_run, float& alpha, float (&bias)[8]) {
+  constexpr int kMaskVal = kMaskedS + (kBiased ? kMagicI : 0);
   if constexpr (kMasked) {
 #pragma unroll
     for (int c = 0; c < 128; ++c)
-      if (c > lim) s[c] = (uint32_t)kMaskedS;
+      if (c > lim) s[c] = (uint32_t)kMaskVal;
   }
-  // integer max per k-scale class, then 8 dequantised candidates
+  // integer max per k-scale class (the bias keeps the order), then 8 dequantised candidates
   int mx[8];
 #pragma unroll
-  for (int k = 0; k < 8; ++k) mx[k] = kMaskedS;
+  for (int k = 0; k < 8; ++k) mx[k] = kMaskVal;
 #pragma unroll
   for (int c = 0; c < 128; ++c) mx[kcls(c)] = max(mx[kcls(c)], (int)s[c]);
   float mrow = -1e30f;
 #pragma unroll
   for (int k = 0; k < 8; ++k) {
     // a class whose columns are all masked must not win the max
-    float cand = (float)mx[k] * sc[k];
-    if constexpr (kMasked) cand = (mx[k] == kMaskedS) ? -1e30f : cand;
+    float cand = (kBiased ? (__int_as_float(mx[k]) - kMagicF) : (float)mx[k]) * sc[k];
+    if constexpr (kMasked) cand = (mx[k] == kMaskVal) ? -1e30f : cand;
     mrow = fmaxf(mrow, cand);
   }
   const bool grow = mrow > m_run + (kFp8 ? kFp8Tau : kF16Tau);
@@ -85,17 +93,31 @@ __device__ __forceinline__ void unpack2(uint64_t v, float& lo, float& hi);
 #define SAGE_POLY_DEN 4
 #endif
 
+__device__ __forceinline__ uint64_t ffma2(uint64_t a, uint64_t b, uint64_t c);
+__device__ __forceinline__ uint64_t fadd2(uint64_t a, uint64_t b);
+
+#ifndef SAGE_PACKED
+#define SAGE_PACKED 1  // dequant FFMA and row-sum FADD as packed f32x2 instructions (half the issue slots); 0: scalar
+#endif
+
 // Phase 2: p = 2^(s * sc + bias) in place; returns the row sum of this tile.
-template <bool kMasked, int kLo = 0, int kHi = 128, int kDeg = 3>
+template <bool kMasked, int kLo = 0, int kHi = 128, int kDeg = 3, bool kBiased = false>
 __device__ __forceinline__ float softmax_exp(uint32_t (&s)[128], const float (&sc)[8],
                                              const float (&bias)[8], int lim) {
   float dsum0 = 0.f, dsum1 = 0.f;
+  uint64_t dsum2 = 0;
 #pragma unroll
   for (int c = kLo; c < kHi; c += 2) {
-    float x0 = __int_as_float((int)s[c] + kMagicI);
-    float x1 = __int_as_float((int)s[c + 1] + kMagicI);
-    float y0 = fmaf(x0, sc[kcls(c)], bias[kcls(c)]);
-    float y1 = fmaf(x1, sc[kcls(c + 1)], bias[kcls(c + 1)]);
+    float x0 = __int_as_float((int)s[c] + (kBiased ? 0 : kMagicI));
+    float x1 = __int_as_float((int)s[c + 1] + (kBiased ? 0 : kMagicI));
+    float y0, y1;
+    if (SAGE_PACKED) {
+      // columns c and c+1 share their k-scale class
+      unpack2(ffma2(pack2(x0, x1), pack2(sc[kcls(c)], sc[kcls(c)]), pack2(bias[kcls(c)], bias[kcls(c)])), y0, y1);
+    } else {
+      y0 = fmaf(x0, sc[kcls(c)], bias[kcls(c)]);
+      y1 = fmaf(x1, sc[kcls(c + 1)], bias[kcls(c + 1)]);
+    }
     float p0, p1;
     if (((c >> 1) % SAGE_POLY_DEN) < SAGE_POLY_NUM) {
       unpack2(exp2_poly2<kDeg>(pack2(y0, y1)), p0, p1);
@@ -107,11 +129,16 @@ __device__ __forceinline__ float softmax_exp(uint32_t (&s)[128], const float (&s
       p0 = (c > lim) ? 0.f : p0;
       p1 = (c + 1 > lim) ? 0.f : p1;
     }
-    dsum0 += p0;
-    dsum1 += p1;
+    if (SAGE_PACKED) {
+      dsum2 = fadd2(dsum2, pack2(p0, p1));
+    } else {
+      dsum0 += p0;
+      dsum1 += p1;
+    }
     s[c] = __float_as_uint(p0);
     s[c + 1] = __float_as_uint(p1);
   }
+  if (SAGE_PACKED) unpack2(dsum2, dsum0, dsum1);
   return dsum0 + dsum1;
 }
 
