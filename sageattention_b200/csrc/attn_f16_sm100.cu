@@ -2,15 +2,17 @@
 //
 // Replaces the reference's mma.sync kernel
 //   qk_int_sv_f16_attn_kernel  (/root/reference/csrc/qattn/qk_int_sv_f16_cuda_sm80.cu:44-671)
-// Same from-scratch tcgen05 design as attn_sm100.cu (two 128-row Q tiles per CTA, TMA producer warp,
-// single-thread MMA issuer, two softmax warpgroups with one thread per query row, lazy O rescale,
-// setmaxnreg 232/40), with ONE difference that was measured to pay for f16 P (4-5 %): P_t is written
-// back over the consumed S_t columns in TMEM with tcgen05.st and read by the PV MMA as its TMEM A
-// operand, instead of going through a shared-memory tile.  An f16 P tile is 32 KB per Q tile and
-// step; through shared memory it costs 64 KB of st.shared plus 64 KB of extra MMA operand reads per
-// step pair on a port the tensor pipe already saturates, which outweighs the PV(j) + S(j+1) wait the
-// aliasing brings back (issue order PV0(j) S0(j+1) PV1(j) S1(j+1)).  For e4m3 P (half the bytes) the
-// balance tips the other way, see attn_sm100.cu and tools/experiments/README.md.
+// Same from-scratch tcgen05 design as attn_sm100.cu (persistent grid with a dynamic work scheduler,
+// two 128-row Q tiles per work item, TMA producer warp, single-thread MMA issuer, two softmax
+// warpgroups with one thread per query row, lazy O rescale, setmaxnreg 232/40, TMA-store epilogue),
+// with ONE difference that was measured to pay for f16 P (4-5 %): P_t is written back over the
+// consumed S_t columns in TMEM with tcgen05.st and read by the PV MMA as its TMEM A operand, instead
+// of going through a shared-memory tile.  An f16 P tile is 32 KB per Q tile and step; through shared
+// memory it costs 64 KB of st.shared plus 64 KB of extra MMA operand reads per step pair on a port
+// the tensor pipe already saturates, which outweighs the PV(j) + S(j+1) wait the aliasing brings back
+// (issue order PV0(j) S0(j+1) PV1(j) S1(j+1); the tensor pipe executes in order, so S_t(j+1) cannot
+// overtake the P.V that still reads P_t(j)).  For e4m3 P (half the bytes) the balance tips the other
+// way, see attn_sm100.cu and tools/experiments/README.md.
 //
 // TMEM map (512 columns):  S0 [0,128)  S1 [128,256)  O0 [256,256+D)  O1 [256+D,256+2D);
 // P_t aliases the first 64 columns of S_t.  Numerics contract: as attn_sm100.cu.
@@ -21,6 +23,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
+#include <atomic>
 
 #include "../../include/sage_b200.h"
 #include "ptx_sm100.cuh"
@@ -30,9 +33,10 @@
 namespace sage_f16 {
 using namespace sage;
 
-// Development aid (-DSAGE_TRACE, tools/trace_attn.py): SM-clock stamps of CTA (0,0,0)'s pipeline.
+// Development aid (-DSAGE_TRACE, tools/trace_attn.py): SM-clock stamps of CTA 0's first kv steps
+// (counted across its work items; slots 8/9 = last P.V seen / end of the item's epilogue).
 #ifdef SAGE_TRACE
-constexpr int kTraceSteps = 48, kTraceSlots = 8;
+constexpr int kTraceSteps = 64, kTraceSlots = 12;
 __device__ long long g_trace[3][kTraceSteps][kTraceSlots];
 #define SAGE_STAMP(who, j, slot)                                                             \
   do {                                                                                       \
@@ -42,23 +46,19 @@ __device__ long long g_trace[3][kTraceSteps][kTraceSlots];
 #define SAGE_STAMP(who, j, slot) do { } while (0)
 #endif
 
-// 0 = the two softmax warpgroups run freely, 2 = whole softmax steps alternate (see attn_sm100.cu)
-#ifndef SAGE_TURN
+// The two softmax warpgroups run freely here (alternating their exp phases was measured slower with P
+// in TMEM).
 #define SAGE_TURN 0
-#endif
-
-// Development aid: warpgroup 1 starts its first step this many SM cycles late (phase offset
-// between the two softmax warpgroups without any per-step barrier).
-#ifndef SAGE_DELAY
-#define SAGE_DELAY 0
-#endif
 
 constexpr int kTileQ = 128;       // rows per Q tile (= TMEM lanes)
 constexpr int kTileKV = 128;      // kv rows per step
+constexpr int kQStages = 2;      // Q tiles of the current and of the next work item
 constexpr int kKStages = 2;
 constexpr int kVStages = 2;
 constexpr int kSoftmaxThreads = 256;  // 2 warpgroups
 constexpr int kThreads = 384;         // + a third warpgroup: TMA warp, MMA warp, two idle warps
+// setmaxnreg: the launch gives every warp 168 registers; the third warpgroup hands most of its
+// share to the softmax warpgroups, whose exp loop needs the headroom to keep many logits in flight.
 constexpr int kSoftmaxRegs = 232;
 constexpr int kIssueRegs = 40;
 struct AttnKernelParams {
@@ -75,6 +75,9 @@ struct AttnKernelParams {
   int gran;                                      // 1 per_block(128/64) 2 per_warp 3 per_thread
   int warp_q;                                    // 16 or 32 rows per q-scale group (gran 2/3)
   int causal;
+  int n_qpairs;  // ceil(Nq / 256)
+  int n_work;    // work items: B * Hq * n_qpairs
+  unsigned int* sched_counter;  // zero at launch; see g_sched_counter
   int out_bf16;
   float sm_scale_log2;
 };
@@ -85,50 +88,174 @@ struct SmemLayout {
   static constexpr int kKBytes = kTileKV * D;                           // int8
   static constexpr int kVBytes = kFp8 ? D * kTileKV : kTileKV * D * 2;  // e4m3 [D][128] | f16 [128][D]
   static constexpr int kQOff = 0;
-  static constexpr int kKOff = kQOff + 2 * kQBytes;
+  static constexpr int kKOff = kQOff + kQStages * 2 * kQBytes;
   static constexpr int kVOff = kKOff + kKStages * kKBytes;
-  static constexpr int kBarOff = kVOff + kVStages * kVBytes;
-  static constexpr int kNumBars = 1 + 2 * kKStages + 2 * kVStages + 2 + 2 + 2;
+  static constexpr int kPBytes = 0;  // P lives in TMEM
+  static constexpr int kPOff = kVOff + kVStages * kVBytes;
+  static constexpr int kOBytes = kTileQ * D * 2;  // output staging tile per warpgroup: D/64 blocks of [128][128 B], SW128
+  static constexpr int kOOff = kPOff + 2 * kPBytes;
+  static constexpr int kBarOff = kOOff + 2 * kOBytes;
+  static constexpr int kNumBars = 2 * kQStages + 2 * kKStages + 2 * kVStages + 3 * 2 + 2 * 3 /*work ring*/;
   static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
-  static constexpr int kTotal = kTmemPtrOff + 16;
+  static constexpr int kRingOff = kTmemPtrOff + 16;  // work ring: kSchedSlots x 16 B
+  static constexpr int kVsOff = kRingOff + 4 * 16;    // v_scale [D] f32 of every ring slot (bulk-copied by the producer)
+  static constexpr int kTotal = kVsOff + 3 * 128 * 4;
   static constexpr int kDynamic = kTotal + 1024;  // slack for 1024B alignment
 };
 
-// Softmax warpgroup body for Q tile `t` (128 threads, thread = query row).
+// ---------------------------------------------------------------------------------------------
+// Persistent work list with a dynamic scheduler.  A work item is one pair of Q tiles (256 query rows)
+// of one (batch, head).  The TMA producer thread owns the list: a CTA's first item is blockIdx.x,
+// every further one comes from an atomic counter (fetched one item ahead, so its latency is hidden),
+// is decoded there (the integer divisions stay off the softmax warps) and published to the other
+// warps through a small shared-memory ring guarded by mbarriers.
+//   non-causal: w -> (bh = w / n_qpairs, q_pair = w % n_qpairs): neighbours in time share K/V in L2
+//   causal:     heads in groups of kHeadGroup; inside a group the heavy (late) q pairs come first, so
+//               the list is longest-processing-time-first where it matters (the tail of the launch)
+//               while only a few heads' K/V are live in L2 at a time.
+constexpr int kSchedSlots = 3;
+constexpr int kHeadGroup = 8;
+constexpr int kSchedCounters = 1024;
+// One counter per launch in flight (the host rotates through them); the CTA that draws the last
+// ticket of a launch puts the counter back to zero.
+__device__ unsigned int g_sched_counter[kSchedCounters];
+
+struct __align__(16) WorkItem {
+  int q_pair, h, b, hkv;  // q_pair < 0: end of the list
+};
+__device__ __forceinline__ WorkItem decode_work(const AttnKernelParams& p, unsigned int w) {
+  WorkItem o;
+  if (w >= (unsigned int)p.n_work) {
+    o.q_pair = -1; o.h = 0; o.b = 0; o.hkv = 0;
+    return o;
+  }
+  int bh, qp;
+  if (!p.causal) {
+    bh = (int)w / p.n_qpairs;
+    qp = (int)w - bh * p.n_qpairs;
+  } else {
+    const int per_group = kHeadGroup * p.n_qpairs;
+    const int g = (int)w / per_group;
+    const int r = (int)w - g * per_group;
+    const int gsz = min(kHeadGroup, p.B * p.Hq - g * kHeadGroup);
+    const int level = r / gsz;
+    qp = p.n_qpairs - 1 - level;
+    bh = g * kHeadGroup + (r - level * gsz);
+  }
+  o.q_pair = qp;
+  o.b = bh / p.Hq;
+  o.h = bh - o.b * p.Hq;
+  o.hkv = o.h / (p.Hq / p.Hkv);
+  return o;
+}
+// consumer side of the ring (the slot stays valid until this thread arrives on sched_empty)
+__device__ __forceinline__ WorkItem read_work(const WorkItem* ring, uint64_t* sched_full, uint32_t it) {
+  mbar_wait(&sched_full[it % kSchedSlots], (it / kSchedSlots) & 1u);
+  const int4 v = ld_shared_v4(smem_u32(&ring[it % kSchedSlots]));
+  WorkItem o;
+  o.q_pair = v.x; o.h = v.y; o.b = v.z; o.hkv = v.w;
+  return o;
+}
+// kv tiles per q tile (causal: stop at the diagonal tile; top-left aligned as the reference,
+// /root/reference/csrc/qattn/qk_int_sv_f16_cuda_sm80.cu:218-222)
+__device__ __forceinline__ void item_iters(const AttnKernelParams& p, int q_pair, int (&n_it)[2]) {
+#pragma unroll
+  for (int t = 0; t < 2; ++t) {
+    const int qs = (q_pair * 2 + t) * kTileQ;
+    int kv_end = p.Nk;
+    if (p.causal) kv_end = min(kv_end, qs + kTileQ);
+    n_it[t] = (qs < p.Nq) ? (kv_end + kTileKV - 1) / kTileKV : 0;
+  }
+}
+
+// Running barrier phases of one softmax warpgroup across work items.
+struct WgState {
+  uint32_t steps;    // kv steps this warpgroup has finished (phase of s_full / p_full)
+  uint32_t items;    // work items it has finished (phase of o_full)
+  bool granted;      // warpgroup 1: the first exp turn of the coming item is already granted
+};
+
+// What the step loop of one work item needs; prepared ahead of time (under the previous item's last
+// P.V) so that the global-load latency of the scales is off the item-to-item critical path.
+struct ItemCtx {
+  bool valid;
+  int n_iter;      // kv steps of this warpgroup's tile (0: tile is beyond Nq)
+  int n_pingpong;  // steps both warpgroups execute
+  bool next_pingpong;
+  int q_row;
+  float qs;        // q scale of the row (raw: the load is still in flight when setup returns)
+  const float* ksp;
+};
+template <int D>
+__device__ __forceinline__ ItemCtx softmax_setup(const AttnKernelParams& p, int t, int row,
+                                                 const WorkItem* ring, uint64_t* sched_full, uint32_t it) {
+  ItemCtx c;
+  const WorkItem wi = read_work(ring, sched_full, it);
+  c.valid = wi.q_pair >= 0;
+  c.n_iter = c.n_pingpong = 0;
+  c.next_pingpong = false;
+  c.q_row = 0;
+  c.qs = 0.f;
+  c.ksp = nullptr;
+  if (!c.valid) return c;
+  int n_it[2];
+  item_iters(p, wi.q_pair, n_it);
+  c.n_iter = n_it[t];
+  c.n_pingpong = min(n_it[0], n_it[1]);
+  {  // will both warpgroups alternate in the next item?  (the producer publishes one item ahead)
+    const WorkItem nx = read_work(ring, sched_full, it + 1);
+    if (nx.q_pair >= 0) {
+      int n_nx[2];
+      item_iters(p, nx.q_pair, n_nx);
+      c.next_pingpong = min(n_nx[0], n_nx[1]) > 0;
+    }
+  }
+  c.q_row = (wi.q_pair * 2 + t) * kTileQ + row;
+  {
+    const int sh = (p.warp_q == 16) ? 4 : 5;
+    int idx;
+    if (p.gran == 3) idx = (c.q_row >> sh) * 8 + (c.q_row & 7);
+    else if (p.gran == 2) idx = c.q_row >> sh;
+    else idx = c.q_row >> 7;
+    idx = min(idx, p.q_scale_per_bh - 1);
+    c.qs = __ldg(p.q_scale + (size_t)(wi.b * p.Hq + wi.h) * p.q_scale_per_bh + idx);  // first use: step 0
+  }
+  c.ksp = p.k_scale + (size_t)(wi.b * p.Hkv + wi.hkv) * p.k_scale_per_bh;
+  prefetch_l1(c.ksp);
+  return c;
+}
+
+// The kv steps of one work item for Q tile `t` (128 threads, thread = query row).
 template <int D, bool kFp8>
-__device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int t, int row,
-                                                  int q_tile_start, int n_iter, int b, int h,
-                                                  int hkv, uint32_t tmem_base, uint64_t* s_full,
-                                                  uint64_t* p_full, uint64_t* o_full, int n_pp) {
+__device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, int row,
+                                              const ItemCtx& c, const WorkItem* ring, uint32_t it,
+                                              uint32_t tmem_base, uint64_t* s_full, uint64_t* p_full,
+                                              WgState& st, float& m_out, float& d_out) {
   const int warp_in_wg = (row >> 5);
   const uint32_t lane_off = (uint32_t)(warp_in_wg * 32) << 16;
   const uint32_t tS = tmem_base + lane_off + (uint32_t)(t * 128);
   const uint32_t tO = tmem_base + lane_off + (uint32_t)(256 + t * D);
-  const int q_row = q_tile_start + row;
-
-  // per-row q scale (folded with sm_scale * log2 e)
-  float qs;
-  {
-    int idx;
-    if (p.gran == 3) idx = (q_row / p.warp_q) * 8 + (q_row & 7);
-    else if (p.gran == 2) idx = q_row / p.warp_q;
-    else idx = q_row / 128;
-    idx = min(idx, p.q_scale_per_bh - 1);
-    qs = p.q_scale[(size_t)(b * p.Hq + h) * p.q_scale_per_bh + idx] * p.sm_scale_log2;
-  }
-  const float* ksp = p.k_scale + (size_t)(b * p.Hkv + hkv) * p.k_scale_per_bh;
+  const int q_row = c.q_row;
+  const float qs = c.qs * p.sm_scale_log2;  // folded with sm_scale * log2 e
+  const float* ksp = c.ksp;
+  const int n_iter = c.n_iter, n_pingpong = c.n_pingpong;
+  const bool next_pingpong = c.next_pingpong;
 
   float m_run = -1e30f, d_run = 0.f;
-  if (SAGE_TURN == 2 && t == 1 && n_pp > 0) named_bar_arrive(1, 2 * kTileQ);
+  // named barrier 1: "warpgroup 0 may start exp", named barrier 2: "warpgroup 1 may start exp".
+  // Only the first n_pingpong steps of an item, which both warpgroups execute, take part.  Warpgroup 1
+  // grants warpgroup 0's first turn of an item either here or, when it can, right after its own last
+  // exp phase of the previous item (so that warpgroup 0 does not wait for warpgroup 1's epilogue).
+  if (SAGE_TURN != 0 && t == 1 && n_pingpong > 0) {
+    if (!st.granted) named_bar_arrive(1, 2 * kTileQ);
+    st.granted = false;
+  }
 #ifdef SAGE_TRACE
-  const bool trace_on = (blockIdx.x | blockIdx.y | blockIdx.z) == 0 && row == 0;
+  const bool trace_on = blockIdx.x == 0 && row == 0;
 #endif
 
-  if (SAGE_DELAY > 0 && t == 1) {
-    const long long t_go = clock64() + SAGE_DELAY;
-    while (clock64() < t_go) __nanosleep(100);
-  }
   for (int j = 0; j < n_iter; ++j) {
+    const uint32_t ph = st.steps & 1u;
     // k scales of this tile -> 8 class scales
     float sc[8];
 #pragma unroll
@@ -140,11 +267,10 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
       idx = min(idx, p.k_scale_per_bh - 1);
       sc[k] = __ldg(ksp + idx) * qs;
     }
-    SAGE_STAMP(t, j, 0);
-    mbar_wait(&s_full[t], j & 1);
-    if (SAGE_TURN == 2 && j < n_pp) named_bar_sync(1 + t, 2 * kTileQ);
+    SAGE_STAMP(t, st.steps, 0);
+    mbar_wait(&s_full[t], ph);
     tc_fence_after();
-    SAGE_STAMP(t, j, 1);
+    SAGE_STAMP(t, st.steps, 1);
     uint32_t s[128];
     {
       uint32_t(&s0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
@@ -157,10 +283,12 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
       tmem_ld32(tS + 96, s3);
       tc_wait_ld();
     }
-    SAGE_STAMP(t, j, 2);
+    SAGE_STAMP(t, st.steps, 2);
     if (p.debug_s != nullptr && j == 0) {
       const int nq_pad = (p.Nq + 255) / 256 * 256;
-      int* dst = p.debug_s + ((size_t)(b * p.Hq + h) * nq_pad + q_row) * 128;
+      const int4 wv = ld_shared_v4(smem_u32(&ring[it % kSchedSlots]));
+      WorkItem wi; wi.h = wv.y; wi.b = wv.z;
+      int* dst = p.debug_s + ((size_t)(wi.b * p.Hq + wi.h) * nq_pad + q_row) * 128;
 #pragma unroll
       for (int c = 0; c < 128; ++c) dst[c] = (int)s[c];
     }
@@ -168,26 +296,47 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
     int lim = p.Nk - 1 - kv0;
     if (p.causal) lim = min(lim, q_row - kv0);
     const bool masked_tile = (j == n_iter - 1) && (p.causal || (p.Nk - kv0) < kTileKV);
-    float alpha, bias[8];
+    float alpha, bias[8], dsum;
     uint32_t w[kFp8 ? 32 : 64];
-    if (masked_tile) softmax_max<kFp8, true>(s, sc, lim, m_run, alpha, bias);
-    else softmax_max<kFp8, false>(s, sc, 127, m_run, alpha, bias);
-    const float dsum = masked_tile ? softmax_exp<true>(s, sc, bias, lim) : softmax_exp<false>(s, sc, bias, 127);
-    d_run = fmaf(d_run, alpha, dsum);
-    softmax_pack<kFp8>(s, w);
-    // rescale O when some row of this warp moved its max (PV(j-1) is complete: S(j) was issued
-    // after it and tcgen05.commit tracks all earlier MMAs)
-    if (j > 0 && __any_sync(0xffffffffu, alpha != 1.0f)) {
-#pragma unroll
-      for (int c0 = 0; c0 < D; c0 += 32) {
-        uint32_t o[32];
-        tmem_ld32(tO + c0, o);
-        tc_wait_ld();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-        tmem_st32(tO + c0, o);
+    if (masked_tile) softmax_max<kFp8, true, false>(s, sc, lim, m_run, alpha, bias);
+    else softmax_max<kFp8, false, false>(s, sc, 127, m_run, alpha, bias);
+    SAGE_STAMP(t, st.steps, 5);
+    // The exp phases of the two warpgroups alternate (they are the only MUFU-bound stretch): each
+    // warpgroup's load / max / pack / store phases then run under the other one's exponentials.
+    if (SAGE_TURN == 1 && j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
+    SAGE_STAMP(t, st.steps, 6);
+    if (masked_tile) dsum = softmax_exp<true, 0, 128, 3, false>(s, sc, bias, lim);
+    else dsum = softmax_exp<false, 0, 128, 3, false>(s, sc, bias, 127);
+    if (SAGE_TURN == 1 && j < n_pingpong) {
+      if (t == 0) {
+        named_bar_arrive(2, 2 * kTileQ);
+      } else if (j < n_pingpong - 1) {
+        named_bar_arrive(1, 2 * kTileQ);
+      } else if (next_pingpong) {
+        named_bar_arrive(1, 2 * kTileQ);
+        st.granted = true;
       }
     }
+    SAGE_STAMP(t, st.steps, 7);
+    d_run = fmaf(d_run, alpha, dsum);
+    softmax_pack<kFp8>(s, w);
+    SAGE_STAMP(t, st.steps, 3);
+    // rescale O when some row of this warp moved its max (PV(j-1) is complete: S(j) was issued after
+    // it and tcgen05.commit tracks all earlier MMAs)
+    if (j > 0) {
+      if (__any_sync(0xffffffffu, alpha != 1.0f)) {
+#pragma unroll
+        for (int c0 = 0; c0 < D; c0 += 32) {
+          uint32_t o[32];
+          tmem_ld32(tO + c0, o);
+          tc_wait_ld();
+#pragma unroll
+          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+          tmem_st32(tO + c0, o);
+        }
+      }
+    }
+    // P row -> TMEM, over the S columns just consumed
     if constexpr (kFp8) {
       tmem_st32(tS, w);
     } else {
@@ -199,52 +348,135 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
     tc_wait_st();
     tc_fence_before();
     mbar_arrive(&p_full[t]);
-    if (SAGE_TURN == 2 && j < n_pp - t) named_bar_arrive(2 - t, 2 * kTileQ);
-    SAGE_STAMP(t, j, 4);
+    SAGE_STAMP(t, st.steps, 4);
+    ++st.steps;
   }
 
-  // ---- epilogue
-  mbar_wait(&o_full[t], 0);
-  tc_fence_after();
-  const float inv_d = rcp_approx(d_run);
-  const bool store = q_row < p.Nq;
+  m_out = m_run;
+  d_out = d_run;
+}
+
+// O row (f32, registers) -> 16-bit row in the 128B-swizzled staging tile.  Packed f32x2 arithmetic:
+// y = o * (1/d) [* v_scale] [+ v_mean], two columns per instruction, one F2FP per pair.
+template <int D, bool kBf16, bool kScale, bool kMean>
+__device__ __forceinline__ void epilogue_convert(const uint32_t (&o)[D], float inv_d, uint32_t vs_addr,
+                                                 const float* vmp, uint32_t orow, uint32_t ox) {
+  const uint64_t inv2 = pack2(inv_d, inv_d);
+#pragma unroll
+  for (int c0 = 0; c0 < D; c0 += 8) {
+    uint32_t packed[4];
+#pragma unroll
+    for (int i = 0; i < 8; i += 4) {
+      uint64_t y0 = fmul2(pack2(__uint_as_float(o[c0 + i]), __uint_as_float(o[c0 + i + 1])), inv2);
+      uint64_t y1 = fmul2(pack2(__uint_as_float(o[c0 + i + 2]), __uint_as_float(o[c0 + i + 3])), inv2);
+      uint64_t s0 = 0, s1 = 0, m0 = 0, m1 = 0;
+      if constexpr (kScale) {
+        const int4 f = ld_shared_v4(vs_addr + (uint32_t)(c0 + i) * 4u);
+        s0 = pack2(__int_as_float(f.x), __int_as_float(f.y));
+        s1 = pack2(__int_as_float(f.z), __int_as_float(f.w));
+      }
+      if constexpr (kMean) {
+        const float4 f = __ldg(reinterpret_cast<const float4*>(vmp + c0 + i));
+        m0 = pack2(f.x, f.y);
+        m1 = pack2(f.z, f.w);
+      }
+      if constexpr (kScale && kMean) {
+        y0 = ffma2(y0, s0, m0);
+        y1 = ffma2(y1, s1, m1);
+      } else if constexpr (kScale) {
+        y0 = fmul2(y0, s0);
+        y1 = fmul2(y1, s1);
+      } else if constexpr (kMean) {
+        y0 = fadd2(y0, m0);
+        y1 = fadd2(y1, m1);
+      }
+      float a0, a1, a2, a3;
+      unpack2(y0, a0, a1);
+      unpack2(y1, a2, a3);
+      if constexpr (kBf16) {
+        __nv_bfloat162 v0 = __floats2bfloat162_rn(a0, a1), v1 = __floats2bfloat162_rn(a2, a3);
+        packed[i >> 1] = *reinterpret_cast<uint32_t*>(&v0);
+        packed[(i >> 1) + 1] = *reinterpret_cast<uint32_t*>(&v1);
+      } else {
+        __half2 v0 = __floats2half2_rn(a0, a1), v1 = __floats2half2_rn(a2, a3);
+        packed[i >> 1] = *reinterpret_cast<uint32_t*>(&v0);
+        packed[(i >> 1) + 1] = *reinterpret_cast<uint32_t*>(&v1);
+      }
+    }
+    // 8 columns = one 16-byte chunk of 64-column block (c0 / 64); chunk c sits at c ^ (row & 7)
+    const uint32_t chunk = (uint32_t)((c0 & 63) >> 3);
+    const uint32_t addr = orow + (uint32_t)(c0 >> 6) * (kTileQ * 128) + ((chunk ^ ox) << 4);
+    st_shared_v4(addr, packed[0], packed[1], packed[2], packed[3]);
+  }
+}
+
+// Epilogue of one work item: O_t / d [* v_scale] [+ v_mean] -> 16-bit -> shared memory -> bulk tensor
+// store; LSE.  The issuer is already running the next item's Q.K^T under it; its first P.V (which
+// overwrites O_t) waits for this warpgroup's next P tile, i.e. for the loads done here.
+template <int D, bool kFp8>
+__device__ __forceinline__ void softmax_epilogue(const AttnKernelParams& p, int t, int row,
+                                                 const WorkItem* ring, uint32_t it, uint32_t tmem_base,
+                                                 uint8_t* o_smem, float* vs_smem, const CUtensorMap* tmO,
+                                                 uint64_t* o_full, WgState& st, float m_run, float d_run) {
+  const uint32_t tO = tmem_base + ((uint32_t)((row >> 5) * 32) << 16) + (uint32_t)(256 + t * D);
+  // the item's coordinates come back from the ring slot (still owned by this thread) instead of
+  // living in registers through the step loop
+  const int4 wv = ld_shared_v4(smem_u32(&ring[it % kSchedSlots]));
+  const int h = wv.y, b = wv.z, hkv = wv.w;
+  const int q_tile_start = (wv.x * 2 + t) * kTileQ;
+  const int q_row = q_tile_start + row;
+#ifdef SAGE_TRACE
+  const bool trace_on = blockIdx.x == 0 && row == 0;
+#endif
   const float* vsp = p.v_scale ? p.v_scale + (size_t)(b * p.Hkv + hkv) * D : nullptr;
   const float* vmp = p.v_mean ? p.v_mean + (size_t)(b * p.Hkv + hkv) * D : nullptr;
-  uint16_t* optr = reinterpret_cast<uint16_t*>(p.o) + (size_t)b * p.o_stride_b +
-                   (size_t)h * p.o_stride_h + (size_t)q_row * p.o_stride_n;
+  // per-channel factors: v_scale sits in the ring slot (bulk-copied by the producer together with the
+  // entry); the rarer v_mean is only prefetched here and read chunk by chunk below
+  if (vmp && (row & 31) < D / 32) prefetch_l1(vmp + (row & 31) * 32);
+  SAGE_STAMP(t, st.steps - 1, 10);
+  mbar_wait(&o_full[t], st.items & 1u);
+  ++st.items;
+  tc_fence_after();
+  SAGE_STAMP(t, st.steps - 1, 8);
+  const float inv_d = rcp_approx(d_run);
+  // The tile goes out through shared memory and ONE bulk tensor store per 64-column block (a thread
+  // owns a row, so direct stores would be 16 bytes per thread at a row pitch: measured 5-7 k cycles
+  // per item).  The previous item's store must have finished reading the staging tile first.
+  if (row == 0) tma_store_wait_read();
+  named_bar_sync(3 + t, kTileQ);
+  SAGE_STAMP(t, st.steps - 1, 11);
+  const uint32_t orow = smem_u32(o_smem) + (uint32_t)row * 128u;
+  const uint32_t ox = (uint32_t)(row & 7);
+  // all of O_t in one go: the four loads overlap, one wait
+  uint32_t oall[D];
 #pragma unroll
-  for (int c0 = 0; c0 < D; c0 += 32) {
-    uint32_t o[32];
-    tmem_ld32(tO + c0, o);
-    tc_wait_ld();
-    uint32_t packed[16];
-#pragma unroll
-    for (int i = 0; i < 32; i += 2) {
-      float x0 = __uint_as_float(o[i]) * inv_d;
-      float x1 = __uint_as_float(o[i + 1]) * inv_d;
-      if (vsp) {
-        x0 *= __ldg(vsp + c0 + i);
-        x1 *= __ldg(vsp + c0 + i + 1);
-      }
-      if (vmp) {
-        x0 += __ldg(vmp + c0 + i);
-        x1 += __ldg(vmp + c0 + i + 1);
-      }
-      if (p.out_bf16) {
-        __nv_bfloat162 v = __floats2bfloat162_rn(x0, x1);
-        packed[i >> 1] = *reinterpret_cast<uint32_t*>(&v);
-      } else {
-        __half2 v = __floats2half2_rn(x0, x1);
-        packed[i >> 1] = *reinterpret_cast<uint32_t*>(&v);
-      }
-    }
-    if (store) {
-      uint4* dst = reinterpret_cast<uint4*>(optr + c0);
-#pragma unroll
-      for (int i = 0; i < 4; ++i)
-        dst[i] = make_uint4(packed[4 * i], packed[4 * i + 1], packed[4 * i + 2], packed[4 * i + 3]);
-    }
+  for (int c0 = 0; c0 < D; c0 += 32)
+    tmem_ld32(tO + c0, *reinterpret_cast<uint32_t(*)[32]>(&oall[c0]));
+  tc_wait_ld();
+  // one specialised conversion loop per (output type, v_scale?, v_mean?) instead of per-element selects
+  const uint32_t vs_addr = smem_u32(vs_smem);
+  const int variant = (p.out_bf16 ? 4 : 0) | (vsp ? 2 : 0) | (vmp ? 1 : 0);
+  switch (variant) {
+    case 0: epilogue_convert<D, false, false, false>(oall, inv_d, vs_addr, vmp, orow, ox); break;
+    case 1: epilogue_convert<D, false, false, true>(oall, inv_d, vs_addr, vmp, orow, ox); break;
+    case 2: epilogue_convert<D, false, true, false>(oall, inv_d, vs_addr, vmp, orow, ox); break;
+    case 3: epilogue_convert<D, false, true, true>(oall, inv_d, vs_addr, vmp, orow, ox); break;
+    case 4: epilogue_convert<D, true, false, false>(oall, inv_d, vs_addr, vmp, orow, ox); break;
+    case 5: epilogue_convert<D, true, false, true>(oall, inv_d, vs_addr, vmp, orow, ox); break;
+    case 6: epilogue_convert<D, true, true, false>(oall, inv_d, vs_addr, vmp, orow, ox); break;
+    default: epilogue_convert<D, true, true, true>(oall, inv_d, vs_addr, vmp, orow, ox); break;
   }
+  fence_proxy_async_smem();
+  named_bar_sync(3 + t, kTileQ);
+  if (row == 0) {
+#pragma unroll
+    for (int c = 0; c < D / 64; ++c)
+      tma_store_4d(tmO, o_smem + c * (kTileQ * 128), c * 64, q_tile_start, h, b);
+    tma_store_commit();
+  }
+  const bool store = q_row < p.Nq;
+  tc_fence_before();
+  SAGE_STAMP(t, st.steps - 1, 9);
   if (p.lse && store)
     p.lse[(size_t)(b * p.Hq + h) * p.Nq + q_row] =
         lg2_approx(d_run) + m_run - (kFp8 ? kFp8Offset : 0.f);
@@ -254,49 +486,41 @@ __device__ __forceinline__ void softmax_warpgroup(const AttnKernelParams& p, int
 template <int D, bool kFp8>
 __global__ void __launch_bounds__(kThreads, 1)
 sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
-                     const __grid_constant__ CUtensorMap tmV, const AttnKernelParams p) {
+                     const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
+                     const AttnKernelParams p) {
   using L = SmemLayout<D, kFp8>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + L::kBarOff);
-  uint64_t* q_full = bars;                    // 1
-  uint64_t* k_full = q_full + 1;              // kKStages
+  uint64_t* q_full = bars;                    // kQStages
+  uint64_t* q_empty = q_full + kQStages;      // kQStages
+  uint64_t* k_full = q_empty + kQStages;      // kKStages
   uint64_t* k_empty = k_full + kKStages;      // kKStages
   uint64_t* v_full = k_empty + kKStages;      // kVStages
   uint64_t* v_empty = v_full + kVStages;      // kVStages
   uint64_t* s_full = v_empty + kVStages;      // 2
   uint64_t* p_full = s_full + 2;              // 2
   uint64_t* o_full = p_full + 2;              // 2
+  uint64_t* sched_full = o_full + 2;          // kSchedSlots
+  uint64_t* sched_empty = sched_full + kSchedSlots;
+  WorkItem* ring = reinterpret_cast<WorkItem*>(smem + L::kRingOff);
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(smem + L::kTmemPtrOff);
 
   const int warp = threadIdx.x >> 5;
-  // heavy (late) q tiles first: helps the causal tail
-  const int q_pair = (int)gridDim.x - 1 - (int)blockIdx.x;
-  const int h = blockIdx.y, b = blockIdx.z;
-  const int hkv = h / (p.Hq / p.Hkv);
-  const int q_start = q_pair * 2 * kTileQ;
-
-  // kv tiles per q tile (causal: stop at the diagonal tile; top-left aligned as the reference,
-  // /root/reference/csrc/qattn/qk_int_sv_f16_cuda_sm80.cu:218-222)
-  int n_it[2];
-#pragma unroll
-  for (int t = 0; t < 2; ++t) {
-    const int qs = q_start + t * kTileQ;
-    int kv_end = p.Nk;
-    if (p.causal) kv_end = min(kv_end, qs + kTileQ);
-    n_it[t] = (qs < p.Nq) ? (kv_end + kTileKV - 1) / kTileKV : 0;
-  }
-  const int n_max = max(n_it[0], n_it[1]);
 
   if (threadIdx.x == 0) {
-    mbar_init(q_full, 1);
+    for (int i = 0; i < kQStages; ++i) { mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], 1); }
     for (int i = 0; i < kKStages; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); }
     for (int i = 0; i < kVStages; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
     for (int t = 0; t < 2; ++t) {
       mbar_init(&s_full[t], 1);
       mbar_init(&p_full[t], kTileQ);
       mbar_init(&o_full[t], 1);
+    }
+    for (int i = 0; i < kSchedSlots; ++i) {
+      mbar_init(&sched_full[i], 1);
+      mbar_init(&sched_empty[i], kSoftmaxThreads + 1);  // every softmax thread + the MMA issuer
     }
     fence_barrier_init();
   }
@@ -305,6 +529,7 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       tma_prefetch_desc(&tmQ);
       tma_prefetch_desc(&tmK);
       tma_prefetch_desc(&tmV);
+      tma_prefetch_desc(&tmO);
     }
   }
   if (warp == 9) tmem_alloc<512>(tmem_ptr);
@@ -312,39 +537,99 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
+#ifdef SAGE_STAGGER
+  {  // experiment: take the CTAs out of lockstep
+    const long long t_go = clock64() + (long long)(blockIdx.x % 8) * SAGE_STAGGER;
+    while (clock64() < t_go) { }
+  }
+#endif
 
   if (warp < 8) {
     // ======================= softmax warpgroups =======================
     reg_alloc<kSoftmaxRegs>();
     const int t = warp >> 2;
     const int row = threadIdx.x & 127;
-    if (n_it[t] > 0)
-      softmax_warpgroup<D, kFp8>(p, t, row, q_start + t * kTileQ, n_it[t], b, h, hkv, tmem_base,
-                                 s_full, p_full, o_full, min(n_it[0], n_it[1]));
+    WgState st{0u, 0u, false};
+    uint32_t it = 0;
+    ItemCtx c = softmax_setup<D>(p, t, row, ring, sched_full, it);
+    while (c.valid) {
+      float m_run = 0.f, d_run = 1.f;
+      if (c.n_iter > 0)
+        softmax_steps<D, kFp8>(p, t, row, c, ring, it, tmem_base, s_full, p_full, st, m_run,
+                               d_run);
+      // the next item is prepared under this item's last P.V
+      const bool had_steps = c.n_iter > 0;
+      c = softmax_setup<D>(p, t, row, ring, sched_full, it + 1);
+      if (had_steps)
+        softmax_epilogue<D, kFp8>(p, t, row, ring, it, tmem_base, smem + L::kOOff + t * L::kOBytes,
+                                  reinterpret_cast<float*>(smem + L::kVsOff) + (it % kSchedSlots) * 128, &tmO, o_full, st, m_run, d_run);
+      mbar_arrive(&sched_empty[it % kSchedSlots]);
+      ++it;
+    }
+    if (row == 0) tma_store_wait_read();  // the staging tile must outlive the last bulk store's reads
   } else if (warp == 8) {
     // ======================= TMA producer =======================
     reg_dealloc<kIssueRegs>();
     if (elect_one()) {
-      mbar_arrive_expect_tx(q_full, 2 * L::kQBytes);
-      tma_load_4d(smem + L::kQOff, &tmQ, q_full, 0, q_start, h, b);
-      tma_load_4d(smem + L::kQOff + L::kQBytes, &tmQ, q_full, 0, q_start + kTileQ, h, b);
-      for (int j = 0; j < n_max; ++j) {
-        const int ks = j % kKStages, vs = j % kVStages;
-        mbar_wait(&k_empty[ks], ((j / kKStages) & 1) ^ 1);
-        mbar_arrive_expect_tx(&k_full[ks], L::kKBytes);
-        tma_load_4d(smem + L::kKOff + ks * L::kKBytes, &tmK, &k_full[ks], 0, j * kTileKV, hkv, b);
-        mbar_wait(&v_empty[vs], ((j / kVStages) & 1) ^ 1);
-        mbar_arrive_expect_tx(&v_full[vs], L::kVBytes);
-        uint8_t* vdst = smem + L::kVOff + vs * L::kVBytes;
-        if constexpr (kFp8) {
-          // V^T e4m3 [D rows][128 kv] (kv contiguous)
-          tma_load_4d(vdst, &tmV, &v_full[vs], j * kTileKV, 0, hkv, b);
+      uint32_t ip = 0, kc = 0, vc = 0;
+      auto publish = [&](uint32_t idx, const WorkItem& w) {
+        const uint32_t slot = idx % kSchedSlots;
+        mbar_wait(&sched_empty[slot], ((idx / kSchedSlots) & 1u) ^ 1u);
+        st_shared_v4(smem_u32(&ring[slot]), (uint32_t)w.q_pair, (uint32_t)w.h, (uint32_t)w.b, (uint32_t)w.hkv);
+        if (p.v_scale != nullptr && w.q_pair >= 0) {
+          // the item's per-channel V scales travel with the ring entry (same barrier)
+          mbar_arrive_expect_tx(&sched_full[slot], D * 4);
+          bulk_load_1d(smem + L::kVsOff + slot * 512, p.v_scale + (size_t)(w.b * p.Hkv + w.hkv) * D, D * 4,
+                       &sched_full[slot]);
         } else {
-          // V f16 [128 kv][D]: one 64-wide (128 B) column block per load
-#pragma unroll
-          for (int c = 0; c < D / 64; ++c)
-            tma_load_4d(vdst + c * (kTileKV * 128), &tmV, &v_full[vs], c * 64, j * kTileKV, hkv, b);
+          mbar_arrive(&sched_full[slot]);
         }
+      };
+      WorkItem cur = decode_work(p, blockIdx.x);
+      publish(0, cur);
+      while (cur.q_pair >= 0) {
+        // ticket of the NEXT item: issued now, consumed after this item's first loads are on their way
+        const unsigned int ticket = atomicAdd(p.sched_counter, 1u);
+        int n_it[2];
+        item_iters(p, cur.q_pair, n_it);
+        const int n_max = max(n_it[0], n_it[1]);
+        const int hkv = cur.hkv;
+        const int q_start = cur.q_pair * 2 * kTileQ;
+        const uint32_t qb = ip % kQStages;
+        mbar_wait(&q_empty[qb], ((ip / kQStages) & 1u) ^ 1u);
+        mbar_arrive_expect_tx(&q_full[qb], 2 * L::kQBytes);
+        uint8_t* qdst = smem + L::kQOff + qb * 2 * L::kQBytes;
+        tma_load_4d(qdst, &tmQ, &q_full[qb], 0, q_start, cur.h, cur.b);
+        tma_load_4d(qdst + L::kQBytes, &tmQ, &q_full[qb], 0, q_start + kTileQ, cur.h, cur.b);
+        WorkItem nxt;
+        for (int j = 0; j < n_max; ++j) {
+          const uint32_t ks = kc % kKStages, vs = vc % kVStages;
+          mbar_wait(&k_empty[ks], ((kc / kKStages) & 1u) ^ 1u);
+          mbar_arrive_expect_tx(&k_full[ks], L::kKBytes);
+          tma_load_4d(smem + L::kKOff + ks * L::kKBytes, &tmK, &k_full[ks], 0, j * kTileKV, hkv, cur.b);
+          mbar_wait(&v_empty[vs], ((vc / kVStages) & 1u) ^ 1u);
+          mbar_arrive_expect_tx(&v_full[vs], L::kVBytes);
+          uint8_t* vdst = smem + L::kVOff + vs * L::kVBytes;
+          if constexpr (kFp8) {
+            // V^T e4m3 [D rows][128 kv] (kv contiguous)
+            tma_load_4d(vdst, &tmV, &v_full[vs], j * kTileKV, 0, hkv, cur.b);
+          } else {
+            // V f16 [128 kv][D]: one 64-wide (128 B) column block per load
+#pragma unroll
+            for (int c = 0; c < D / 64; ++c)
+              tma_load_4d(vdst + c * (kTileKV * 128), &tmV, &v_full[vs], c * 64, j * kTileKV, hkv, cur.b);
+          }
+          ++kc;
+          ++vc;
+          if (j == 0) {
+            // the launch's last ticket puts the counter back for the next launch
+            if (ticket == (unsigned int)p.n_work - 1u) *p.sched_counter = 0u;
+            nxt = decode_work(p, gridDim.x + ticket);
+            publish(ip + 1, nxt);
+          }
+        }
+        ++ip;
+        cur = nxt;
       }
     }
   } else if (warp == 9) {
@@ -362,69 +647,105 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       const uint32_t sK = smem_u32(smem + L::kKOff);
       const uint32_t sV = smem_u32(smem + L::kVOff);
 
-      auto issue_qk = [&](int t, int j) {
-        const uint32_t a0 = sQ + t * L::kQBytes;
-        const uint32_t b0 = sK + (j % kKStages) * L::kKBytes;
+      uint32_t im = 0, kc = 0, vc = 0;  // items started, K tiles consumed, V tiles consumed
+      uint32_t np[2] = {0, 0};          // PV_t issued so far
+
+      // S_t = Q_t.K^T of the K tile in ring slot (kc % stages).  No "S drained" barrier is needed: the
+      // issuer only gets here after it has issued the P.V that reads P_t (which the warpgroup wrote
+      // after pulling S_t into registers), and the tensor pipe executes in order.
+      auto issue_qk = [&](int t, uint32_t qb) {
+        const uint32_t a0 = sQ + (qb * 2 + t) * L::kQBytes;
+        const uint32_t b0 = sK + (kc % kKStages) * L::kKBytes;
 #pragma unroll
         for (int kk = 0; kk < D / 32; ++kk) {
           const uint64_t ad = make_smem_desc(a0 + kk * 32, 16, qk_sbo, qk_swz);
           const uint64_t bd = make_smem_desc(b0 + kk * 32, 16, qk_sbo, qk_swz);
           mma_i8_ss(tmem_base + t * 128, ad, bd, idesc_qk, kk > 0);
         }
+        tc_commit(&s_full[t]);
       };
-      auto issue_pv = [&](int t, int j) {
-        const uint32_t b0 = sV + (j % kVStages) * L::kVBytes;
+      auto issue_pv = [&](int t, bool accumulate) {
+        mbar_wait(&p_full[t], np[t] & 1u);
+        tc_fence_after();
+        const uint32_t b0 = sV + (vc % kVStages) * L::kVBytes;
         const uint32_t d_tmem = tmem_base + 256 + t * D;
         const uint32_t a_tmem = tmem_base + t * 128;
         if constexpr (kFp8) {
 #pragma unroll
           for (int kk = 0; kk < kTileKV / 32; ++kk) {
             const uint64_t bd = make_smem_desc(b0 + kk * 32, 16, 1024, SWZ_128B);
-            mma_f8_ts(d_tmem, a_tmem + kk * 8, bd, idesc_pv, (j > 0) || (kk > 0));
+            mma_f8_ts(d_tmem, a_tmem + kk * 8, bd, idesc_pv, accumulate || (kk > 0));
           }
         } else {
 #pragma unroll
           for (int kk = 0; kk < kTileKV / 16; ++kk) {
             // MN-major B: 16 kv rows x 128 B per MMA = 2 KB step; 64-wide d blocks 16 KB apart
             const uint64_t bd = make_smem_desc(b0 + kk * 2048, kTileKV * 128, 1024, SWZ_128B);
-            mma_f16_ts(d_tmem, a_tmem + kk * 8, bd, idesc_pv, (j > 0) || (kk > 0));
+            mma_f16_ts(d_tmem, a_tmem + kk * 8, bd, idesc_pv, accumulate || (kk > 0));
           }
         }
+        ++np[t];
       };
 
-#ifdef SAGE_TRACE
-      const bool trace_on = (blockIdx.x | blockIdx.y | blockIdx.z) == 0;
-#endif
-      mbar_wait(q_full, 0);
-      mbar_wait(&k_full[0], 0);
-      tc_fence_after();
-      for (int t = 0; t < 2; ++t)
-        if (n_it[t] > 0) { issue_qk(t, 0); tc_commit(&s_full[t]); }
-      tc_commit(&k_empty[0]);
-
-      for (int j = 0; j < n_max; ++j) {
-        mbar_wait(&v_full[j % kVStages], (j / kVStages) & 1);
-        const bool more = (j + 1 < n_max);
+      int n_it[2], n_nx[2];
+      bool have = false;
+      {
+        const WorkItem w0 = read_work(ring, sched_full, 0);
+        mbar_arrive(&sched_empty[0]);
+        have = w0.q_pair >= 0;
+        if (have) {
+          item_iters(p, w0.q_pair, n_it);
+          mbar_wait(&q_full[0], 0);
+          mbar_wait(&k_full[0], 0);
+          tc_fence_after();
 #pragma unroll
-        for (int t = 0; t < 2; ++t) {
-          if (j < n_it[t]) {
-            SAGE_STAMP(2, j, t * 4 + 0);
-            mbar_wait(&p_full[t], j & 1);
-            tc_fence_after();
-            SAGE_STAMP(2, j, t * 4 + 1);
-            issue_pv(t, j);
-            SAGE_STAMP(2, j, t * 4 + 2);
-            if (j == n_it[t] - 1) tc_commit(&o_full[t]);
-          }
-          if (t == 1) tc_commit(&v_empty[j % kVStages]);
-          if (t == 0 && more) {
-            mbar_wait(&k_full[(j + 1) % kKStages], ((j + 1) / kKStages) & 1);
-            tc_fence_after();
-          }
-          if (j + 1 < n_it[t]) { issue_qk(t, j + 1); tc_commit(&s_full[t]); }
-          SAGE_STAMP(2, j, t * 4 + 3);
-          if (t == 1 && more) tc_commit(&k_empty[(j + 1) % kKStages]);
+          for (int t = 0; t < 2; ++t)
+            if (n_it[t] > 0) issue_qk(t, 0);
+          tc_commit(&k_empty[0]);
+          ++kc;
+          if (max(n_it[0], n_it[1]) == 1) tc_commit(&q_empty[0]);
         }
+      }
+      while (have) {
+        const WorkItem wn = read_work(ring, sched_full, im + 1);
+        mbar_arrive(&sched_empty[(im + 1) % kSchedSlots]);
+        const bool have_nxt = wn.q_pair >= 0;
+        if (have_nxt) item_iters(p, wn.q_pair, n_nx);
+        const int n_max = max(n_it[0], n_it[1]);
+        const uint32_t qb = im % kQStages;
+        for (int j = 0; j < n_max; ++j) {
+          mbar_wait(&v_full[vc % kVStages], (vc / kVStages) & 1u);
+          // what follows P_t.V(j) on the tensor pipe: S_t(j+1) of this item, or S_t(0) of the next
+          const bool more = (j + 1 < n_max);
+          const bool cross = !more && have_nxt;
+          const int jn = more ? j + 1 : 0;
+          const int nn0 = more ? n_it[0] : n_nx[0], nn1 = more ? n_it[1] : n_nx[1];
+          const uint32_t qn = more ? qb : (im + 1) % kQStages;
+          if (more || cross) {
+            if (cross) mbar_wait(&q_full[qn], ((im + 1) / kQStages) & 1u);
+            mbar_wait(&k_full[kc % kKStages], (kc / kKStages) & 1u);
+            tc_fence_after();
+          }
+#pragma unroll
+          for (int t = 0; t < 2; ++t) {
+            if (j < n_it[t]) {
+              issue_pv(t, j > 0);
+              if (j == n_it[t] - 1) tc_commit(&o_full[t]);
+            }
+            if (t == 1) tc_commit(&v_empty[vc % kVStages]);
+            if ((more || cross) && jn < (t == 0 ? nn0 : nn1)) issue_qk(t, qn);
+          }
+          ++vc;
+          if (more || cross) {
+            tc_commit(&k_empty[kc % kKStages]);
+            ++kc;
+            if (jn == max(nn0, nn1) - 1) tc_commit(&q_empty[qn]);  // last use of that Q slot
+          }
+        }
+        ++im;
+        n_it[0] = n_nx[0];
+        n_it[1] = n_nx[1];
+        have = have_nxt;
       }
     }
   } else {
@@ -484,10 +805,38 @@ static int make_map4(CUtensorMap* m, CUtensorMapDataType dt, void* ptr, uint64_t
   return 0;
 }
 
+// SMs of the current device (the persistent grid runs one CTA on each)
+static int sm_count() {
+  static int cached[64] = {0};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+// device address of the scheduler counters on the current device
+static unsigned int* sched_counters() {
+  static unsigned int* cached[64] = {nullptr};
+  int dev = 0;
+  cudaGetDevice(&dev);
+  if (dev < 0 || dev >= 64) dev = 0;
+  if (cached[dev] == nullptr) {
+    void* ptr = nullptr;
+    if (cudaGetSymbolAddress(&ptr, g_sched_counter) != cudaSuccess) return nullptr;
+    cached[dev] = static_cast<unsigned int*>(ptr);
+  }
+  return cached[dev];
+}
+
 template <int D, bool kFp8>
 static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
   using L = SmemLayout<D, kFp8>;
-  CUtensorMap tmQ, tmK, tmV;
+  CUtensorMap tmQ, tmK, tmV, tmO;
   const CUtensorMapSwizzle qk_swz = (D == 128) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
   int rc;
   rc = make_map4(&tmQ, CU_TENSOR_MAP_DATA_TYPE_UINT8, a->q8.ptr, D, a->Nq, a->Hq, a->B,
@@ -507,6 +856,11 @@ static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
                    a->v.stride_n * 2, a->v.stride_h * 2, a->v.stride_b * 2, 64, kTileKV,
                    CU_TENSOR_MAP_SWIZZLE_128B, "v_f16");
   }
+  if (rc) return rc;
+  // o rows through TMA: 64-column (128 B) blocks of 128 rows; rows >= Nq are clipped by the hardware
+  rc = make_map4(&tmO, CU_TENSOR_MAP_DATA_TYPE_UINT16, a->o.ptr, D, a->Nq, a->Hq, a->B,
+                 a->o.stride_n * 2, a->o.stride_h * 2, a->o.stride_b * 2, 64, kTileQ,
+                 CU_TENSOR_MAP_SWIZZLE_128B, "o");
   if (rc) return rc;
 
   AttnKernelParams p;
@@ -542,8 +896,18 @@ static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
     SAGE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kDynamic));
     attr_set = true;
   }
-  dim3 grid((a->Nq + 2 * kTileQ - 1) / (2 * kTileQ), a->Hq, a->B);
-  kern<<<grid, kThreads, L::kDynamic, stream>>>(tmQ, tmK, tmV, p);
+  p.n_qpairs = (a->Nq + 2 * kTileQ - 1) / (2 * kTileQ);
+  const long long n_work = (long long)a->B * a->Hq * p.n_qpairs;
+  SAGE_REQUIRE(n_work < (1ll << 31), "too many work items");
+  p.n_work = (int)n_work;
+  {
+    static std::atomic<unsigned int> next_counter{0};
+    unsigned int* base = sched_counters();
+    SAGE_REQUIRE(base != nullptr, "cudaGetSymbolAddress(g_sched_counter) failed");
+    p.sched_counter = base + next_counter.fetch_add(1) % kSchedCounters;
+  }
+  const int grid = (int)(n_work < sm_count() ? n_work : sm_count());
+  kern<<<grid, kThreads, L::kDynamic, stream>>>(tmQ, tmK, tmV, tmO, p);
   SAGE_CUDA(cudaGetLastError());
   return 0;
 }
@@ -563,6 +927,12 @@ static int check_attn_args(const sage_attn_args* a) {
 }
 
 }  // namespace sage_f16
+
+#ifdef SAGE_TRACE
+extern "C" int sage_debug_trace(long long* out) {
+  return (int)cudaMemcpyFromSymbol(out, sage_f16::g_trace, sizeof(sage_f16::g_trace));
+}
+#endif
 
 extern "C" int sage_attn_i8_f16(const sage_attn_args* a, void* stream) {
   int rc = sage_f16::check_attn_args(a);
