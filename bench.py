@@ -42,8 +42,9 @@ WORKLOADS = {
     "wan": ("sageattn", 1, 40, 75600, 128, False, "bfloat16"),
 }
 # dram__bytes_read.sum + dram__bytes_write.sum of the attention kernel, one `ncu --set full` capture
-# per workload (profiles/r1_ncu_attn_f16_c2_summary.txt); algorithmic bytes at C2 fp16 = 402.7e6
-NCU_TRAFFIC = {"c2_fp16": 377.89e6, "c3_fp8": 299.76e6}
+# per workload (profiles/r1b_ncu_attn_f16_c2_summary.txt, r1b_ncu_attn_f8_c3_summary.txt: the persistent
+# kernels); algorithmic bytes at C2 fp16 = 402.7e6
+NCU_TRAFFIC = {"c2_fp16": 377.14e6, "c3_fp8": 302.79e6}
 METRIC = "attention TOPS @hd64/hd128 seq 1K-32K (causal/non-causal), % of INT8/FP8 tensor peak"
 
 

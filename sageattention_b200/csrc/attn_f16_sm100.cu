@@ -30,6 +30,9 @@
 #include "softmax_sm100.cuh"
 #include "status.h"
 
+namespace sage {
+int launch_attn_f16_d64(const sage_attn_args* a, cudaStream_t stream);  // attn_sm100.cu
+}
 namespace sage_f16 {
 using namespace sage;
 
@@ -938,5 +941,10 @@ extern "C" int sage_attn_i8_f16(const sage_attn_args* a, void* stream) {
   int rc = sage_f16::check_attn_args(a);
   if (rc) return rc;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  #ifdef SAGE_F16_D64_OWN
   return a->D == 128 ? sage_f16::launch_attn<128, false>(a, s) : sage_f16::launch_attn<64, false>(a, s);
+#else
+  // head_dim 64: TMEM has room for an un-aliased P, so the shared design of attn_sm100.cu is used
+  return a->D == 128 ? sage_f16::launch_attn<128, false>(a, s) : sage::launch_attn_f16_d64(a, s);
+#endif
 }

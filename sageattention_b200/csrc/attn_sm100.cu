@@ -64,6 +64,14 @@ __device__ long long g_trace[3][kTraceSteps][kTraceSlots];
 #ifndef SAGE_TURN
 #define SAGE_TURN 1
 #endif
+// k scales of later steps prefetched to L1: measured -0.7 %, off.
+#ifndef SAGE_KPREF
+#define SAGE_KPREF 0
+#endif
+
+// P_t in its own TMEM columns (head_dim 64: S 256 + O 128 + P 64/128 columns) or in shared memory
+template <int D>
+constexpr bool kPTmem = (D == 64);
 
 constexpr int kTileQ = 128;       // rows per Q tile (= TMEM lanes)
 constexpr int kTileKV = 128;      // kv rows per step
@@ -105,7 +113,7 @@ struct SmemLayout {
   static constexpr int kQOff = 0;
   static constexpr int kKOff = kQOff + kQStages * 2 * kQBytes;
   static constexpr int kVOff = kKOff + kKStages * kKBytes;
-  static constexpr int kPBytes = kFp8 ? kTileQ * kTileKV : kTileQ * kTileKV * 2;  // K-major, SW128
+  static constexpr int kPBytes = kPTmem<D> ? 0 : (kFp8 ? kTileQ * kTileKV : kTileQ * kTileKV * 2);  // K-major, SW128
   static constexpr int kPOff = kVOff + kVStages * kVBytes;
   static constexpr int kOBytes = kTileQ * D * 2;  // output staging tile per warpgroup: D/64 blocks of [128][128 B], SW128
   static constexpr int kOOff = kPOff + 2 * kPBytes;
@@ -283,6 +291,8 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
       idx = min(idx, p.k_scale_per_bh - 1);
       sc[k] = __ldg(ksp + idx) * qs;
     }
+    // pull the next steps' k scales towards L1 (a 128-byte line holds 4 (per_thread) / 16 steps)
+    if (SAGE_KPREF) prefetch_l1(ksp + min((j + 2) * (p.gran == 3 ? 8 : 2), p.k_scale_per_bh - 1));
     SAGE_STAMP(t, st.steps, 0);
     mbar_wait(&s_full[t], ph);
     tc_fence_after();
@@ -360,7 +370,21 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
         tc_fence_before();
       }
     }
-    {
+    if constexpr (kPTmem<D>) {
+      // head_dim 64 leaves 128 TMEM columns free: P_t gets its own columns there (no shared-memory
+      // store, no proxy fence, and the P.V MMA reads A from TMEM instead of the shared-memory port)
+      const uint32_t tP = tmem_base + lane_off + (uint32_t)(384 + t * (kFp8 ? 32 : 64));
+      if constexpr (kFp8) {
+        tmem_st32(tP, w);
+      } else {
+        uint32_t(&w0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&w[0]);
+        uint32_t(&w1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&w[32]);
+        tmem_st32(tP, w0);
+        tmem_st32(tP + 32, w1);
+      }
+      tc_wait_st();
+      tc_fence_before();
+    } else {
       // P row -> smem, K-major 128B-swizzled (16B chunk c of row r sits at chunk c ^ (r & 7))
       const uint32_t prow = smem_u32(p_smem) + (uint32_t)row * 128u;
       const uint32_t x = (uint32_t)(row & 7);
@@ -369,8 +393,8 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
         const uint32_t addr = prow + (uint32_t)(c >> 3) * (kTileQ * 128) + (((uint32_t)(c & 7) ^ x) << 4);
         st_shared_v4(addr, w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
       }
+      fence_proxy_async_smem();
     }
-    fence_proxy_async_smem();
     mbar_arrive(&p_full[t]);
     SAGE_STAMP(t, st.steps, 4);
     ++st.steps;
@@ -706,21 +730,30 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         const uint32_t a0 = sP + t * L::kPBytes;
         const uint32_t b0 = sV + (vc % kVStages) * L::kVBytes;
         const uint32_t d_tmem = tmem_base + 256 + t * D;
+        const uint32_t a_tmem = tmem_base + 384 + t * (kFp8 ? 32 : 64);  // kPTmem only
         if constexpr (kFp8) {
 #pragma unroll
           for (int kk = 0; kk < kTileKV / 32; ++kk) {
-            const uint64_t ad = make_smem_desc(a0 + kk * 32, 16, 1024, SWZ_128B);
             const uint64_t bd = make_smem_desc(b0 + kk * 32, 16, 1024, SWZ_128B);
-            mma_f8_ss(d_tmem, ad, bd, idesc_pv, accumulate || (kk > 0));
+            if constexpr (kPTmem<D>) {
+              mma_f8_ts(d_tmem, a_tmem + kk * 8, bd, idesc_pv, accumulate || (kk > 0));
+            } else {
+              const uint64_t ad = make_smem_desc(a0 + kk * 32, 16, 1024, SWZ_128B);
+              mma_f8_ss(d_tmem, ad, bd, idesc_pv, accumulate || (kk > 0));
+            }
           }
         } else {
 #pragma unroll
           for (int kk = 0; kk < kTileKV / 16; ++kk) {
-            // A: two 64-wide K blocks of [128 rows][128 B], 16 KB apart, 32 B per MMA inside a block
-            const uint64_t ad = make_smem_desc(a0 + (kk >> 2) * (kTileQ * 128) + (kk & 3) * 32, 16, 1024, SWZ_128B);
             // MN-major B: 16 kv rows x 128 B per MMA = 2 KB step; 64-wide d blocks 16 KB apart
             const uint64_t bd = make_smem_desc(b0 + kk * 2048, kTileKV * 128, 1024, SWZ_128B);
-            mma_f16_ss(d_tmem, ad, bd, idesc_pv, accumulate || (kk > 0));
+            if constexpr (kPTmem<D>) {
+              mma_f16_ts(d_tmem, a_tmem + kk * 8, bd, idesc_pv, accumulate || (kk > 0));
+            } else {
+              // A: two 64-wide K blocks of [128 rows][128 B], 16 KB apart, 32 B per MMA inside a block
+              const uint64_t ad = make_smem_desc(a0 + (kk >> 2) * (kTileQ * 128) + (kk & 3) * 32, 16, 1024, SWZ_128B);
+              mma_f16_ss(d_tmem, ad, bd, idesc_pv, accumulate || (kk > 0));
+            }
           }
         }
         tc_commit(&p_empty[t]);
@@ -961,6 +994,12 @@ static int check_attn_args(const sage_attn_args* a) {
   return 0;
 }
 
+}  // namespace sage
+
+// head_dim 64 with f16 P also runs on this kernel (P in spare TMEM columns, S(j+1) issued as soon as
+// S(j) is drained); called from sage_attn_i8_f16 in attn_f16_sm100.cu
+namespace sage {
+int launch_attn_f16_d64(const sage_attn_args* a, cudaStream_t stream) { return launch_attn<64, false>(a, stream); }
 }  // namespace sage
 
 #ifdef SAGE_TRACE

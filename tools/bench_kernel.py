@@ -20,9 +20,18 @@ import torch  # noqa: E402
 
 
 def time_fn(fn, reps, warm=5):
-    for _ in range(warm):
+    # warm up for at least 20 ms of device time: a short kernel timed right after a long, power-capped
+    # configuration otherwise reads 20-30 % low (clock recovery), as does the first configuration of a run
+    t0 = torch.cuda.Event(enable_timing=True)
+    t1 = torch.cuda.Event(enable_timing=True)
+    spent, n = 0.0, 0
+    while n < warm or (spent < 20.0 and n < 2000):
+        t0.record()
         fn()
-    torch.cuda.synchronize()
+        t1.record()
+        torch.cuda.synchronize()
+        spent += t0.elapsed_time(t1)
+        n += 1
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
     for a, b in evs:
         a.record()
