@@ -64,6 +64,11 @@ __device__ long long g_trace[3][kTraceSteps][kTraceSlots];
 #ifndef SAGE_TURN
 #define SAGE_TURN 1
 #endif
+// 1: S(j+1) is pulled into registers under the P store's fence of step j instead of at the top of step
+// j+1.  Measured 6 % SLOWER (hd128 1288 -> 1211, hd64 674 -> 623 TOPS at N=8192), default 0.
+#ifndef SAGE_SPREF
+#define SAGE_SPREF 0
+#endif
 // k scales of later steps prefetched to L1: measured -0.7 %, off.
 #ifndef SAGE_KPREF
 #define SAGE_KPREF 0
@@ -278,6 +283,26 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
   const bool trace_on = blockIdx.x == 0 && row == 0;
 #endif
 
+  uint32_t s[128];
+  auto load_s = [&]() {
+    uint32_t(&s0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
+    uint32_t(&s1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[32]);
+    uint32_t(&s2)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[64]);
+    uint32_t(&s3)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[96]);
+    tmem_ld32(tS + 0, s0);
+    tmem_ld32(tS + 32, s1);
+    tmem_ld32(tS + 64, s2);
+    tmem_ld32(tS + 96, s3);
+  };
+#if SAGE_SPREF
+  // the first S of the item; every later one is pulled in under the previous step's P store
+  mbar_wait(&s_full[t], st.steps & 1u);
+  tc_fence_after();
+  load_s();
+  tc_wait_ld();
+  tc_fence_before();
+  mbar_arrive(&s_free[t]);  // S_t is in registers: the issuer may overwrite it with the next S_t
+#endif
   for (int j = 0; j < n_iter; ++j) {
     const uint32_t ph = st.steps & 1u;
     // k scales of this tile -> 8 class scales
@@ -294,24 +319,16 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
     // pull the next steps' k scales towards L1 (a 128-byte line holds 4 (per_thread) / 16 steps)
     if (SAGE_KPREF) prefetch_l1(ksp + min((j + 2) * (p.gran == 3 ? 8 : 2), p.k_scale_per_bh - 1));
     SAGE_STAMP(t, st.steps, 0);
+#if !SAGE_SPREF
     mbar_wait(&s_full[t], ph);
     tc_fence_after();
     SAGE_STAMP(t, st.steps, 1);
-    uint32_t s[128];
-    {
-      uint32_t(&s0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
-      uint32_t(&s1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[32]);
-      uint32_t(&s2)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[64]);
-      uint32_t(&s3)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[96]);
-      tmem_ld32(tS + 0, s0);
-      tmem_ld32(tS + 32, s1);
-      tmem_ld32(tS + 64, s2);
-      tmem_ld32(tS + 96, s3);
-      tc_wait_ld();
-    }
+    load_s();
+    tc_wait_ld();
     // S_t is in registers: the issuer may overwrite it with the next S_t
     tc_fence_before();
     mbar_arrive(&s_free[t]);
+#endif
     SAGE_STAMP(t, st.steps, 2);
     if (p.debug_s != nullptr && j == 0) {
       const int nq_pad = (p.Nq + 255) / 256 * 256;
@@ -352,24 +369,8 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
     SAGE_STAMP(t, st.steps, 3);
     // PV(j-1) complete: P tile reusable and O_t stable (at j == 0 the epilogue of the previous item
     // has already waited for that item's last PV)
-    if (j > 0) {
-      mbar_wait(&p_empty[t], ph ^ 1u);
-      // rescale O when some row of this warp moved its max
-      if (__any_sync(0xffffffffu, alpha != 1.0f)) {
-        tc_fence_after();
-#pragma unroll
-        for (int c0 = 0; c0 < D; c0 += 32) {
-          uint32_t o[32];
-          tmem_ld32(tO + c0, o);
-          tc_wait_ld();
-#pragma unroll
-          for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-          tmem_st32(tO + c0, o);
-        }
-        tc_wait_st();
-        tc_fence_before();
-      }
-    }
+    if (j > 0) mbar_wait(&p_empty[t], ph ^ 1u);
+    // P leaves the registers first (w[] is dead after this) ...
     if constexpr (kPTmem<D>) {
       // head_dim 64 leaves 128 TMEM columns free: P_t gets its own columns there (no shared-memory
       // store, no proxy fence, and the P.V MMA reads A from TMEM instead of the shared-memory port)
@@ -382,8 +383,6 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
         tmem_st32(tP, w0);
         tmem_st32(tP + 32, w1);
       }
-      tc_wait_st();
-      tc_fence_before();
     } else {
       // P row -> smem, K-major 128B-swizzled (16B chunk c of row r sits at chunk c ^ (r & 7))
       const uint32_t prow = smem_u32(p_smem) + (uint32_t)row * 128u;
@@ -393,9 +392,41 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
         const uint32_t addr = prow + (uint32_t)(c >> 3) * (kTileQ * 128) + (((uint32_t)(c & 7) ^ x) << 4);
         st_shared_v4(addr, w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
       }
+    }
+    // ... then O is rescaled when some row of this warp moved its max ...
+    if (j > 0 && __any_sync(0xffffffffu, alpha != 1.0f)) {
+      tc_fence_after();
+#pragma unroll
+      for (int c0 = 0; c0 < D; c0 += 32) {
+        uint32_t o[32];
+        tmem_ld32(tO + c0, o);
+        tc_wait_ld();
+#pragma unroll
+        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+        tmem_st32(tO + c0, o);
+      }
+    }
+    // ... and the logits of the NEXT step (ready long ago: their MMA went out when this step's S was
+    // drained) start their way into the s[] registers, under the fences and the barrier traffic.
+    const bool s_pref = SAGE_SPREF && (j + 1 < n_iter);
+    if (s_pref) {
+      mbar_wait(&s_full[t], ph ^ 1u);
+      tc_fence_after();
+      load_s();
+    }
+    if constexpr (kPTmem<D>) {
+      tc_wait_st();
+    } else {
+      tc_wait_st();  // the rescale's stores (no-op otherwise)
       fence_proxy_async_smem();
     }
+    tc_fence_before();
     mbar_arrive(&p_full[t]);
+    if (s_pref) {
+      tc_wait_ld();
+      tc_fence_before();
+      mbar_arrive(&s_free[t]);
+    }
     SAGE_STAMP(t, st.steps, 4);
     ++st.steps;
   }
