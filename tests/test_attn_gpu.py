@@ -209,3 +209,70 @@ def test_host_pipeline_matches_direct_calls():
     for i in range(steps):
         ref = sb.sageattn_qk_int8_pv_fp16_cuda(hq[i].cuda(), hk[i].cuda(), hv[i].cuda(), is_causal=bool(i & 1))
         assert torch.equal(outs[i], ref.cpu()), f"step {i}"
+
+
+def _random_codes(b, hq, hk, nq, nk, d, pv, seed):
+    """int8 Q/K codes with random scales and a V in the kernel's input format (kernel-level inputs, as
+    the reference's kernel benches build them: bench/bench_qk_int8_pv_fp8_cuda.py:72-98)."""
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    q8 = torch.randint(-95, 95, (b, hq, nq, d), dtype=torch.int8, device=DEV, generator=g)
+    k8 = torch.randint(-95, 95, (b, hk, nk, d), dtype=torch.int8, device=DEV, generator=g)
+    qs = torch.rand(b, hq, (nq + 127) // 128 * 4 * 8, device=DEV, generator=g) * 0.01 + 0.005
+    ks = torch.rand(b, hk, (nk + 63) // 64 * 4, device=DEV, generator=g) * 0.01 + 0.005
+    if pv == "f8":
+        npad = (nk + 127) // 128 * 128
+        v = torch.randn(b, hk, d, npad, device=DEV, generator=g).to(torch.float8_e4m3fn)
+        vs = torch.rand(b, hk, d, device=DEV, generator=g) + 0.5
+    else:
+        v = torch.randn(b, hk, nk, d, device=DEV, generator=g).to(torch.float16)
+        vs = None
+    return q8, qs, k8, ks, v, vs
+
+
+@pytest.mark.parametrize("pv", ["f8", "f16"])
+@pytest.mark.parametrize("d", [128, 64])
+@pytest.mark.parametrize("causal", [False, True])
+def test_persistent_grid_matches_one_item_per_cta(pv, d, causal):
+    """Size-independent property of the persistent kernels: with more work items than SMs (every CTA
+    walks several items through the dynamic scheduler, the Q/K/V rings and the output staging tile
+    carry over from item to item) each (batch, head) must come out BIT-identical to a launch that holds
+    this head alone (at most a few items, one per CTA) - and a second launch must repeat the first (the
+    scheduler counter is reset by the launch itself)."""
+    b, hq, hk, n = 3, 24, 12, 1536 + 40            # 7 q pairs x 72 heads = 504 items on 148 SMs; GQA; ragged tail
+    q8, qs, k8, ks, v, vs = _random_codes(b, hq, hk, n, n, d, pv, seed=11 + d)
+    sm = d ** -0.5
+    o1, l1 = run_kernel(pv, q8, qs, k8, ks, v, vs, None, 3, causal, sm, torch.float16, lse=True)
+    o2, l2 = run_kernel(pv, q8, qs, k8, ks, v, vs, None, 3, causal, sm, torch.float16, lse=True)
+    torch.cuda.synchronize()
+    assert torch.equal(o1, o2) and torch.equal(l1, l2)
+    assert torch.isfinite(o1.float()).all()
+    for bi, hi in [(0, 0), (1, 7), (2, 23), (0, 13)]:
+        hk_i = hi // (hq // hk)
+        sl = lambda t, h: t[bi:bi + 1, h:h + 1].contiguous()
+        o_s, l_s = run_kernel(pv, sl(q8, hi), sl(qs, hi), sl(k8, hk_i), sl(ks, hk_i), sl(v, hk_i),
+                              None if vs is None else sl(vs, hk_i), None, 3, causal, sm, torch.float16, lse=True)
+        assert torch.equal(o_s[0, 0], o1[bi, hi]), (bi, hi)
+        assert torch.equal(l_s[0, 0], l1[bi, hi]), (bi, hi)
+
+
+@pytest.mark.parametrize("pv", ["f8", "f16"])
+def test_kernel_in_cuda_graph(pv):
+    """The launch is capturable (no allocation, no host synchronisation inside the C ABI call; the scheduler
+    counter it points at resets itself), and a replayed graph reproduces the eager result every time."""
+    q8, qs, k8, ks, v, vs = _random_codes(2, 16, 16, 2048, 2048, 128, pv, seed=5)   # 256 items
+    sm = 128 ** -0.5
+    o_ref = run_kernel(pv, q8, qs, k8, ks, v, vs, None, 3, True, sm, torch.float16)
+    o = torch.empty_like(o_ref)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        core._launch(pv == "f8", q8, k8, v, o, qs, ks, vs, None, "HND", True, 3, 32, sm, False)  # warm-up
+    torch.cuda.current_stream().wait_stream(s)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        core._launch(pv == "f8", q8, k8, v, o, qs, ks, vs, None, "HND", True, 3, 32, sm, False)
+    for _ in range(3):
+        o.zero_()
+        g.replay()
+        torch.cuda.synchronize()
+        assert torch.equal(o, o_ref)
