@@ -19,9 +19,12 @@ sys.path.insert(0, ROOT)
 import torch  # noqa: E402
 
 
-def time_fn(fn, reps, warm=5):
+def time_fn(fn, reps, warm=5, graph=True):
+    """Median / best device time of one fn() in ms.  Launches are replayed from a CUDA graph (several per
+    replay when they are short) so that the number is the GPU's, not the Python caller's: one operator
+    launch costs the host 60-100 us, more than the kernel itself takes at N <= 2K."""
     # warm up for at least 20 ms of device time: a short kernel timed right after a long, power-capped
-    # configuration otherwise reads 20-30 % low (clock recovery), as does the first configuration of a run
+    # configuration otherwise reads low (clock recovery), as does the first configuration of a run
     t0 = torch.cuda.Event(enable_timing=True)
     t1 = torch.cuda.Event(enable_timing=True)
     spent, n = 0.0, 0
@@ -32,13 +35,28 @@ def time_fn(fn, reps, warm=5):
         torch.cuda.synchronize()
         spent += t0.elapsed_time(t1)
         n += 1
+    inner, run = 1, fn
+    if graph:
+        try:
+            inner = 8 if spent / n < 1.0 else 1
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                for _ in range(inner):
+                    fn()
+            run = g.replay
+            run()
+            torch.cuda.synchronize()
+        except Exception as e:  # launches outside the capturing stream etc.: time the calls directly
+            print("graph capture failed, timing direct calls:", type(e).__name__, file=sys.stderr)
+            torch.cuda.synchronize()
+            inner, run = 1, fn
     evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(reps)]
     for a, b in evs:
         a.record()
-        fn()
+        run()
         b.record()
     torch.cuda.synchronize()
-    ts = sorted(a.elapsed_time(b) for a, b in evs)
+    ts = sorted(a.elapsed_time(b) / inner for a, b in evs)
     return ts[len(ts) // 2], ts[0]
 
 
@@ -111,10 +129,10 @@ def main():
                 if args.baselines:
                     if ref80 is not None and n <= 16384:
                         fn = lambda: ref80.qk_int8_sv_f16_accum_f32_attn(q8, k8, v, o, qs, ks, 1, int(causal), gran, sm, 0)
-                        med, best = time_fn(fn, max(5, args.reps // 3))
+                        med, best = time_fn(fn, max(5, args.reps // 3), graph=False)
                         emit(dict(impl="ref_sm80_f32", d=d, causal=causal, n=n, ms=med, tops=flops / med * 1e-9))
                         fn = lambda: ref80.qk_int8_sv_f16_accum_f16_attn(q8, k8, v, o, qs, ks, 1, int(causal), gran, sm, 0)
-                        med, best = time_fn(fn, max(5, args.reps // 3))
+                        med, best = time_fn(fn, max(5, args.reps // 3), graph=False)
                         emit(dict(impl="ref_sm80_f16", d=d, causal=causal, n=n, ms=med, tops=flops / med * 1e-9))
                     qb = torch.randn(B, n, H, d, dtype=torch.bfloat16, device=dev)
                     kb = torch.randn(B, n, H, d, dtype=torch.bfloat16, device=dev)
