@@ -196,6 +196,8 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--sp", default="heads", choices=["heads", "ulysses"],
                     help="DiT workloads under torchrun: head sharding (no collective) or Ulysses all-to-all")
+    ap.add_argument("--sp-chunks", type=int, default=1,
+                    help="Ulysses: groups of heads whose all-to-alls overlap the attention of another group")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
@@ -236,6 +238,7 @@ def main():
         shape = (b, n_loc, h, d)
         base_fn = fn
         fn = lambda q_, k_, v_, is_causal=False: parallel.ulysses_sageattn(q_, k_, v_, attn_fn=base_fn,
+                                                                           head_chunks=args.sp_chunks,
                                                                            is_causal=is_causal)
         n = n_loc * world
     else:
@@ -330,7 +333,7 @@ def main():
         "ms_per_step": t_ms, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
         "dtype": "int8+fp8" if fp8 else "int8+fp16", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {api} B={b} H={h} N={n} D={d} causal={causal} {dtype_name}, "
-                               f"heads per rank {h_loc}" + (", Ulysses all-to-all (NCCL)" if ulysses else ""),
+                               f"heads per rank {h_loc}" + (f", Ulysses all-to-all (NCCL), {args.sp_chunks} head group(s) pipelined" if ulysses else ""),
                    "l2": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2" % (4 * nbytes / 1e6)},
         "e2e": {"value": e2e_val, "unit": "TOPS", "h2d_bytes_per_step": 3 * nbytes * world,
                 "d2h_bytes_per_step": nbytes * world, "ms_per_step": e2e_ms},

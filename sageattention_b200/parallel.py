@@ -7,7 +7,9 @@ operator is independent, so two layouts cover the named DiT configs:
 * Ulysses (`ulysses_sageattn`): activations arrive sequence-sharded [B, N/P, H, D]; ONE all-to-all
   scatters heads / gathers the sequence for q, k, v together, the operator runs on H/P heads of the
   FULL sequence (so K smoothing, scales and therefore numerics are identical to one GPU), and one
-  all-to-all brings O back to [B, N/P, H, D].  NCCL over NVLink/NVSwitch on GPUs; the same code runs
+  all-to-all brings O back to [B, N/P, H, D].  With B = 1 the rank's heads can be pipelined in groups
+  (`head_chunks`; measured neutral with NCCL, whose kernels need the SMs the persistent attention grid
+  holds - DESIGN 5).  NCCL over NVLink/NVSwitch on GPUs; the same code runs
   over gloo on CPU tensors for the host-logic tests (with a stand-in attention function).
 """
 from typing import Callable, Optional
@@ -48,12 +50,98 @@ def _head_to_seq_shard(x: torch.Tensor, group, world: int) -> torch.Tensor:
     return recv.permute(1, 2, 0, 3, 4).reshape(b, n, world * hp, d)
 
 
+def _a2a_heads_in(x: torch.Tensor, lo: int, hi: int, group, world: int) -> torch.Tensor:
+    """Batch-1 path in: heads [lo, hi) of EVERY rank's head block, [1, n_loc, H, D] ->
+    [1, n_loc*P, hi-lo, D].  One copy (the head gather into the send buffer); the receive buffer,
+    chunked by source rank = by sequence block, already IS the head-sharded tensor."""
+    _, n, h, d = x.shape
+    hp = h // world
+    send = torch.empty((world, n, hi - lo, d), dtype=x.dtype, device=x.device)
+    send.copy_(x.view(n, world, hp, d)[:, :, lo:hi].transpose(0, 1))
+    recv = torch.empty_like(send)
+    dist.all_to_all_single(recv, send, group=group)
+    return recv.view(1, world * n, hi - lo, d)
+
+
+def _a2a_heads_out(o: torch.Tensor, group, world: int) -> torch.Tensor:
+    """Batch-1 path back: [1, n_loc*P, hc, D] (contiguous: it is its own send buffer, chunk p = sequence
+    block p) -> [P, n_loc, hc, D], chunk p = these heads as computed by rank p."""
+    _, nt, hc, d = o.shape
+    recv = torch.empty((world, nt // world, hc, d), dtype=o.dtype, device=o.device)
+    dist.all_to_all_single(recv, o.view(world, nt // world, hc, d), group=group)
+    return recv
+
+
+_COMM_STREAMS = {}
+
+
+def _ulysses_b1(q, k, v, group, world, attn_fn, head_chunks, kwargs):
+    """B = 1 (the DiT case).  The rank's heads are processed in `head_chunks` groups: all inbound
+    all-to-alls are queued on a side stream, attention on group c starts as soon as ITS q/k/v have
+    arrived and runs under the transfers of group c+1, and its output travels back under the attention of
+    the next group.  4 tensor copies in total (11 in the generic path)."""
+    n, h, d = q.shape[1:]
+    hk = k.size(2)
+    hp, hkp = h // world, hk // world
+    g = h // hk
+    chunks = max(1, min(head_chunks, hkp))
+    bounds = [(hkp * c) // chunks for c in range(chunks + 1)]  # kv-head ranges; q heads follow (GQA)
+    cuda = q.is_cuda
+    if cuda:
+        cur = torch.cuda.current_stream(q.device)
+        comm = _COMM_STREAMS.get(q.device)
+        if comm is None:
+            comm = _COMM_STREAMS[q.device] = torch.cuda.Stream(q.device)
+        comm.wait_stream(cur)
+    ins = []
+    for c in range(chunks):
+        lo, hi = bounds[c], bounds[c + 1]
+        if cuda:
+            with torch.cuda.stream(comm):
+                t = tuple(_a2a_heads_in(x, a, b_, group, world)
+                          for x, a, b_ in ((q, lo * g, hi * g), (k, lo, hi), (v, lo, hi)))
+                ev = torch.cuda.Event()
+                ev.record(comm)
+            for x in t:
+                x.record_stream(cur)
+        else:
+            t = (_a2a_heads_in(q, lo * g, hi * g, group, world), _a2a_heads_in(k, lo, hi, group, world),
+                 _a2a_heads_in(v, lo, hi, group, world))
+            ev = None
+        ins.append((t, ev))
+    out = torch.empty((1, n, h, d), dtype=q.dtype, device=q.device)
+    outs = []
+    for c, ((qh, kh, vh), ev) in enumerate(ins):
+        if cuda:
+            cur.wait_event(ev)
+        o = attn_fn(qh, kh, vh, tensor_layout="NHD", **kwargs).contiguous()
+        if cuda:
+            done = torch.cuda.Event()
+            done.record(cur)
+            o.record_stream(comm)
+            with torch.cuda.stream(comm):
+                comm.wait_event(done)
+                r = _a2a_heads_out(o, group, world)
+            r.record_stream(cur)
+        else:
+            r = _a2a_heads_out(o, group, world)
+        outs.append(r)
+    if cuda:
+        cur.wait_stream(comm)
+    ov = out.view(n, world, hp, d)
+    for c, r in enumerate(outs):
+        ov[:, :, bounds[c] * g:bounds[c + 1] * g].copy_(r.transpose(0, 1))  # head interleave of the received chunks
+    return out
+
+
 def ulysses_sageattn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, group=None,
-                     attn_fn: Optional[Callable] = None, **kwargs) -> torch.Tensor:
+                     attn_fn: Optional[Callable] = None, head_chunks: int = 1, **kwargs) -> torch.Tensor:
     """Sequence-parallel attention.  q, k, v: this rank's sequence block, "NHD" layout
     [B, N/P, H, D] (all ranks hold equally long blocks; pad the sequence to a multiple of P first).
     Returns this rank's block of the output, [B, N/P, H, D].  kwargs go to the attention function
-    (default: sageattn); `tensor_layout` is fixed to "NHD" and `return_lse` is not supported here."""
+    (default: sageattn); `tensor_layout` is fixed to "NHD" and `return_lse` is not supported here.
+    `head_chunks`: with B = 1, how many groups the rank's heads are split into so that the all-to-alls of
+    one group overlap the attention of another (1 = no overlap)."""
     if kwargs.pop("return_lse", False):
         raise ValueError("ulysses_sageattn does not return the LSE")
     kwargs.pop("tensor_layout", None)
@@ -65,6 +153,9 @@ def ulysses_sageattn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, group=No
     h = q.size(2)
     if h % world or k.size(2) % world:
         raise ValueError(f"head counts ({h}, {k.size(2)}) must be divisible by the world size {world}")
+    if q.size(0) == 1 and k.size(0) == 1 and all(t.is_contiguous() for t in (q, k, v)):
+        # the DiT case (B = 1): communication pipelined against attention over groups of heads
+        return _ulysses_b1(q, k, v, group, world, attn_fn, head_chunks, kwargs)
     if k.size(2) == h and k.shape == q.shape:
         qkv = _seq_to_head_shard(torch.stack((q, k, v)), group, world)  # one collective for all three
         qh, kh, vh = qkv[0], qkv[1], qkv[2]

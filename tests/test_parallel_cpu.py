@@ -20,12 +20,12 @@ def _sdpa_nhd(q, k, v, tensor_layout="NHD", is_causal=False, **kw):
     return o.transpose(1, 2)
 
 
-def _worker(rank, world, port, hq, hk, q_out):
+def _worker(rank, world, port, hq, hk, q_out, b=2):
     os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         g = torch.Generator().manual_seed(0)
-        b, n, d = 2, 24, 16
+        n, d = 24, 16
         q = torch.randn(b, n, hq, d, generator=g)
         k = torch.randn(b, n, hk, d, generator=g)
         v = torch.randn(b, n, hk, d, generator=g)
@@ -44,12 +44,12 @@ def _worker(rank, world, port, hq, hk, q_out):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("hq,hk", [(4, 4), (8, 2)])
-def test_ulysses_and_head_sharding_world2(hq, hk):
+@pytest.mark.parametrize("hq,hk,b", [(4, 4, 2), (8, 2, 2), (4, 4, 1), (8, 2, 1)])   # b = 1: the one-copy fast path
+def test_ulysses_and_head_sharding_world2(hq, hk, b):
     ctx = mp.get_context("spawn")
     q_out = ctx.Queue()
-    port = 29500 + (os.getpid() % 2000) + hq
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, hq, hk, q_out)) for r in range(2)]
+    port = 29500 + (os.getpid() % 2000) + hq + 16 * b
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, hq, hk, q_out, b)) for r in range(2)]
     for p in procs:
         p.start()
     res = [q_out.get(timeout=120) for _ in procs]
@@ -57,7 +57,7 @@ def test_ulysses_and_head_sharding_world2(hq, hk):
         p.join(timeout=60)
         assert p.exitcode == 0
     for rank, err, err2, shape in res:
-        assert shape == (2, 12, hq, 16)
+        assert shape == (b, 12, hq, 16)
         assert err < 1e-5, (rank, err)
         assert err2 < 1e-5, (rank, err2)
 

@@ -24,9 +24,12 @@ def _worker(rank, world, port, q_out):
         full = sb.sageattn(q, k, v, tensor_layout="NHD")
         nl = n // world
         sl = slice(rank * nl, (rank + 1) * nl)
-        o = parallel.ulysses_sageattn(q[:, sl].contiguous(), k[:, sl].contiguous(), v[:, sl].contiguous())
-        torch.cuda.synchronize()
-        same = torch.equal(o, full[:, sl])
+        same = True
+        for chunks in (1, 2, 4):   # head groups pipelined against the all-to-alls: same bits every way
+            o = parallel.ulysses_sageattn(q[:, sl].contiguous(), k[:, sl].contiguous(), v[:, sl].contiguous(),
+                                          head_chunks=chunks)
+            torch.cuda.synchronize()
+            same = same and torch.equal(o, full[:, sl])
         ref = torch.nn.functional.scaled_dot_product_attention(q.float().transpose(1, 2), k.float().transpose(1, 2),
                                                                v.float().transpose(1, 2)).transpose(1, 2)[:, sl]
         cos = torch.nn.functional.cosine_similarity(o.float().flatten(), ref.flatten(), dim=0).item()
