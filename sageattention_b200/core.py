@@ -14,7 +14,7 @@ from typing import Any, Optional
 import torch
 
 from . import _lib
-from .quant import (_dims, _dtype_code, _require_cuda, _stream, per_channel_fp8, per_thread_int8,
+from .quant import (_dims, _dtype_code, _require_cuda, _stream, per_block_int8, per_channel_fp8, per_thread_int8,
                     per_warp_int8, prepass_qk_int8, quant_q_int8, seq_mean, smooth_quant_k_int8, sub_mean)
 
 _LOG2E = 1.44269504
@@ -250,3 +250,66 @@ def sageattn(
     return sageattn_qk_int8_pv_fp8_cuda(q, k, v, tensor_layout=tensor_layout, is_causal=is_causal,
                                         sm_scale=sm_scale, pv_accum_dtype="fp32+fp32", smooth_k=smooth_k,
                                         return_lse=return_lse)
+
+
+@torch.compiler.disable
+def sageattn_varlen(
+    q: torch.Tensor,
+    k: torch.Tensor,
+    v: torch.Tensor,
+    cu_seqlens_q: torch.Tensor,
+    cu_seqlens_k: torch.Tensor,
+    max_seqlen_q: int,
+    max_seqlen_k: int,
+    is_causal: bool = False,
+    sm_scale: Optional[float] = None,
+    smooth_k: bool = True,
+    **kwargs: Any,
+) -> torch.Tensor:
+    """Packed variable-length batches (reference core.py:363-477): q [Tq, Hq, D], k / v [Tk, Hkv, D],
+    cu_seqlens_* [batch + 1]; returns [Tq, Hq, D].
+
+    Same scheme as the reference: K is smoothed by its mean over ALL tokens of the pack (core.py:462),
+    Q/K are quantised per block (128 / 64 rows, Q pre-scaled by sm_scale * log2 e, blocks restart at every
+    sequence as in triton/quant_per_block_varlen.py:60), V is fp16, P.V accumulates in fp32.  First version
+    of this entry point: every sequence runs through the fixed-length sm_100a kernels on
+    views of the packed tensors (per-block quantiser launch + attention launch per sequence, output written
+    in place into the packed result), so it costs one host synchronisation for the sequence lengths and
+    3 launches per sequence; a single-launch work list over cu_seqlens is the next step."""
+    dtype = q.dtype
+    assert q.is_cuda, "Input tensors must be on cuda."
+    assert dtype in [torch.float16, torch.bfloat16], \
+        "Input tensors must be in dtype of torch.float16 or torch.bfloat16"
+    assert q.device == k.device == v.device, "All tensors must be on the same device."
+    assert q.dtype == k.dtype == v.dtype, "All tensors must have the same dtype."
+    assert q.dim() == 3 and k.dim() == 3 and v.dim() == 3, "q, k, v must be [tokens, heads, head_dim]"
+    head_dim_og = q.size(-1)
+    q, k, v = _pad_head_dim(q, k, v)
+    assert q.stride(-1) == 1 and k.stride(-1) == 1 and v.stride(-1) == 1, "Last dim of qkv must be contiguous."
+    assert cu_seqlens_q.is_contiguous() and cu_seqlens_k.is_contiguous(), \
+        "cu_seqlens_q and cu_seqlens_k must be contiguous."
+    assert cu_seqlens_q.numel() == cu_seqlens_k.numel() and cu_seqlens_q.numel() >= 2
+    if sm_scale is None:
+        sm_scale = head_dim_og ** -0.5
+    v16 = v.to(torch.float16)
+    if smooth_k:
+        k = k - k.mean(dim=0, keepdim=True)  # over all sequences of the pack, in the input dtype (core.py:462-463)
+    bq = cu_seqlens_q.tolist()
+    bk = cu_seqlens_k.tolist()
+    assert bq[-1] == q.size(0) and bk[-1] == k.size(0), "cu_seqlens do not cover the packed tensors"
+    o = torch.empty(q.shape, dtype=dtype, device=q.device)
+    for i in range(len(bq) - 1):
+        q0, q1, k0, k1 = bq[i], bq[i + 1], bk[i], bk[i + 1]
+        if q1 == q0:
+            continue
+        if k1 == k0:
+            o[q0:q1].zero_()
+            continue
+        assert q1 - q0 <= max_seqlen_q and k1 - k0 <= max_seqlen_k, "sequence longer than max_seqlen"
+        qi, ki, vi = q[q0:q1].unsqueeze(0), k[k0:k1].unsqueeze(0), v16[k0:k1].unsqueeze(0)  # [1, n, H, D] "NHD" views
+        q_int8, q_scale, k_int8, k_scale = per_block_int8(qi, ki, None, BLKQ=128, BLKK=64, sm_scale=sm_scale,
+                                                          tensor_layout="NHD")
+        # Q already carries sm_scale * log2 e: the kernel's own factor must be 1
+        _launch(False, q_int8, k_int8, vi, o[q0:q1].unsqueeze(0), q_scale, k_scale, None, None, "NHD", is_causal,
+                _lib.GRAN_PER_BLOCK, 32, 1.0 / 1.44269504088896340736, False)
+    return o[..., :head_dim_og]

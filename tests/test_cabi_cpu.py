@@ -70,6 +70,10 @@ def test_python_api_matches_reference_signatures():
         ("q", E), ("k", E), ("v", E), ("tensor_layout", "HND"), ("is_causal", False),
         ("qk_quant_gran", "per_thread"), ("sm_scale", None), ("pv_accum_dtype", "fp32+fp16"),
         ("smooth_k", True), ("smooth_v", False), ("return_lse", False)]
+    # core.py:363-375
+    assert params(sb.sageattn_varlen) == [
+        ("q", E), ("k", E), ("v", E), ("cu_seqlens_q", E), ("cu_seqlens_k", E), ("max_seqlen_q", E),
+        ("max_seqlen_k", E), ("is_causal", False), ("sm_scale", None), ("smooth_k", True)]
     assert params(sb.per_block_int8) == [("q", E), ("k", E), ("km", None), ("BLKQ", 128), ("BLKK", 64),
                                          ("sm_scale", None), ("tensor_layout", "HND")]
     assert params(sb.per_warp_int8) == [("q", E), ("k", E), ("km", None), ("BLKQ", 128), ("WARPQ", 32),
@@ -82,6 +86,9 @@ def test_no_cpu_fallback():
     q = torch.randn(1, 2, 64, 64, dtype=torch.float16)
     with pytest.raises(AssertionError):
         sb.sageattn(q, q, q)
+    with pytest.raises(AssertionError):
+        cu = torch.tensor([0, 64], dtype=torch.int32)
+        sb.sageattn_varlen(q[0].transpose(0, 1), q[0].transpose(0, 1), q[0].transpose(0, 1), cu, cu, 64, 64)
     with pytest.raises(RuntimeError):
         sb.per_warp_int8(q, q)
     with pytest.raises(RuntimeError):
