@@ -19,6 +19,8 @@
  *   sage_attn_i8_f8              <- _qattn_sm89.qk_int8_sv_f8_accum_* (7 variants, csrc/qattn/pybind_sm89.cpp)
  *   sage_prepass_qk_int8         <- the whole Q/K prologue of the operator with smooth_k (sageattention/core.py:611-632,
  *                                   794-812: k.mean, per_warp_int8 / per_thread_int8 for q and k) in one launch
+ *   sage_prepass_qkv_fp8         <- the whole prologue of the fp8-P.V operator without smooth_v (sageattention/core.py:
+ *                                   794-850: k.mean, per_warp_int8 / per_thread_int8, V padding + per_channel_fp8) in one launch
  *   sage_smooth_quant_k_int8     <- `km = k.mean(dim=seq)` followed by the K half of per_warp_int8 /
  *                                   per_thread_int8 (sageattention/core.py:611-632), fused in one launch
  */
@@ -93,6 +95,16 @@ int sage_prepass_qk_int8(sage_tensor4 q, sage_tensor4 k, sage_tensor4 q_out, sag
                          float* q_scale, float* k_scale, void* k_mean_out, int B, int Hq, int Hkv, int Nq,
                          int Nk, int D, int dtype, int per_thread, int warp_q, int q_scale_per_bh,
                          int k_scale_per_bh, void* stream);
+
+/* The Q/K/V prologue of the fp8-P.V operator (no smooth_v) in one launch: what sage_prepass_qk_int8(q, k) and
+ * sage_per_channel_fp8(v, smooth_v = 0) produce, bit for bit (same arguments; v is [B,Hkv,Nk,D], n_stat as for
+ * sage_per_channel_fp8, no workspace needed). */
+int sage_prepass_qkv_fp8(sage_tensor4 q, sage_tensor4 k, sage_tensor4 q_out, sage_tensor4 k_out,
+                         float* q_scale, float* k_scale, void* k_mean_out, sage_tensor4 v, uint8_t* v_out,
+                         int64_t vo_stride_b, int64_t vo_stride_h, int64_t vo_stride_d, float* v_scale,
+                         int B, int Hq, int Hkv, int Nq, int Nk, int n_stat, int D, int dtype,
+                         int per_thread, int warp_q, int q_scale_per_bh, int k_scale_per_bh,
+                         float scale_max, void* stream);
 
 /* out(f16)[b,h,n,d] = half( x - mean ) in the input type's packed arithmetic. */
 int sage_sub_mean(sage_tensor4 x, const void* mean, sage_tensor4 out, int B, int H, int N, int D,

@@ -15,7 +15,8 @@ import torch
 
 from . import _lib
 from .quant import (_dims, _dtype_code, _require_cuda, _stream, per_block_int8, per_channel_fp8, per_thread_int8,
-                    per_warp_int8, prepass_qk_int8, quant_q_int8, seq_mean, smooth_quant_k_int8, sub_mean)
+                    per_warp_int8, prepass_qk_int8, prepass_qkv_fp8, quant_q_int8, seq_mean, smooth_quant_k_int8,
+                    sub_mean)
 
 _LOG2E = 1.44269504
 
@@ -211,8 +212,6 @@ def sageattn_qk_int8_pv_fp8_cuda(
     assert q.stride(-1) == 1 and k.stride(-1) == 1 and v.stride(-1) == 1, "Last dim of qkv must be contiguous."
     if sm_scale is None:
         sm_scale = head_dim_og ** -0.5
-    q_int8, q_scale, k_int8, k_scale, lse_correction = _quantize_qk(q, k, smooth_k, qk_quant_gran, tensor_layout,
-                                                                    32, return_lse)
     o = torch.empty(q.size(), dtype=dtype, device=q.device)
     if pv_accum_dtype == "fp32+fp32" and smooth_v:
         warnings.warn("pv_accum_dtype is 'fp32+fp32', smooth_v will be ignored.")
@@ -222,10 +221,21 @@ def sageattn_qk_int8_pv_fp8_cuda(
         smooth_v = False
     quant_v_scale_max = 2.25 if pv_accum_dtype == "fp32+fp16" else 448.0
     kv_len = k.size(2) if tensor_layout == "HND" else k.size(1)
-    # the reference zero-pads V to a multiple of 128 tokens first (core.py:822-828); the kernel
-    # reproduces that padding's effect on Npad / the smooth_v mean without the extra copy
-    v_fp8, v_scale, vm = per_channel_fp8(v, tensor_layout=tensor_layout, scale_max=quant_v_scale_max,
-                                         smooth_v=smooth_v, _n_stat=(kv_len + 127) // 128 * 128)
+    # the reference zero-pads V to a multiple of 128 tokens first (core.py:822-828); the kernels
+    # reproduce that padding's effect on Npad / the smooth_v mean without the extra copy
+    n_stat = (kv_len + 127) // 128 * 128
+    if smooth_k and not smooth_v and k.shape == v.shape:
+        # the whole prologue in ONE launch: K slices (mean + quantise), V slices (range + e4m3 transpose) and
+        # Q tiles side by side (bit-identical to the separate launches; measured at C2 in DESIGN 3.2)
+        q_int8, q_scale, k_int8, k_scale, km, v_fp8, v_scale = prepass_qkv_fp8(
+            q, k, v, qk_quant_gran, WARPQ=32, tensor_layout=tensor_layout, scale_max=quant_v_scale_max, _n_stat=n_stat)
+        lse_correction = _lse_correction(q, km, tensor_layout) if return_lse else None
+        vm = None
+    else:
+        q_int8, q_scale, k_int8, k_scale, lse_correction = _quantize_qk(q, k, smooth_k, qk_quant_gran, tensor_layout,
+                                                                        32, return_lse)
+        v_fp8, v_scale, vm = per_channel_fp8(v, tensor_layout=tensor_layout, scale_max=quant_v_scale_max,
+                                             smooth_v=smooth_v, _n_stat=n_stat)
     gran = _lib.GRAN_PER_THREAD if qk_quant_gran == "per_thread" else _lib.GRAN_PER_WARP
     lse = _launch(True, q_int8, k_int8, v_fp8, o, q_scale, k_scale, v_scale, vm, tensor_layout, is_causal, gran,
                   32, sm_scale, return_lse)

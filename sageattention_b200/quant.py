@@ -189,6 +189,46 @@ def prepass_qk_int8(q, k, qk_quant_gran="per_thread", WARPQ=32, tensor_layout="H
     return q_int8, q_scale, k_int8, k_scale, km
 
 
+def prepass_qkv_fp8(q, k, v, qk_quant_gran="per_thread", WARPQ=32, tensor_layout="HND", scale_max=448.0,
+                    _n_stat=None):
+    """The fp8-P.V operator's whole prologue (smooth_k, no smooth_v) in ONE launch.  Returns
+    (q_int8, q_scale, k_int8, k_scale, km, v_fp8, v_scale), identical to prepass_qk_int8(q, k) +
+    per_channel_fp8(v, smooth_v=False): K slices, V slices and Q tiles run side by side in one grid."""
+    _require_cuda(q, k, v)
+    lib = _lib.load()
+    b, hq, nq, d, q4 = _dims(q, tensor_layout)
+    _, hk, nk, _, k4 = _dims(k, tensor_layout)
+    _, hv, nv, _, v4 = _dims(v, tensor_layout)
+    if (hv, nv) != (hk, nk):
+        raise ValueError("k and v must have the same heads and length")
+    per_thread = 1 if qk_quant_gran == "per_thread" else 0
+    q_int8 = torch.empty(q.shape, dtype=torch.int8, device=q.device)
+    k_int8 = torch.empty(k.shape, dtype=torch.int8, device=k.device)
+    _, _, _, _, qo4 = _dims(q_int8, tensor_layout)
+    _, _, _, _, ko4 = _dims(k_int8, tensor_layout)
+    q_per_bh = (nq + 127) // 128 * (128 // WARPQ) * (8 if per_thread else 1)
+    k_per_bh = (nk + 63) // 64 * (4 if per_thread else 1)
+    q_scale = (torch.empty if per_thread or q_per_bh == (nq + WARPQ - 1) // WARPQ else torch.zeros)(
+        (b, hq, q_per_bh), dtype=torch.float32, device=q.device)
+    k_scale = torch.empty((b, hk, k_per_bh), dtype=torch.float32, device=q.device)
+    km = torch.empty((b, hk, d), dtype=k.dtype, device=k.device)
+    n_stat = nk if _n_stat is None else max(nk, int(_n_stat))
+    npad = (n_stat + 63) // 64 * 64
+    if tensor_layout == "HND":
+        v_fp8 = torch.empty((b, hk, d, npad), dtype=torch.float8_e4m3fn, device=v.device)
+        sb, sh, sd = v_fp8.stride(0), v_fp8.stride(1), v_fp8.stride(2)
+    else:
+        v_fp8 = torch.empty((b, d, hk, npad), dtype=torch.float8_e4m3fn, device=v.device)
+        sb, sh, sd = v_fp8.stride(0), v_fp8.stride(2), v_fp8.stride(1)
+    v_scale = torch.empty((b, hk, d), dtype=torch.float32, device=v.device)
+    with torch.cuda.device(q.device):
+        _lib.check(lib.sage_prepass_qkv_fp8(q4, k4, qo4, ko4, q_scale.data_ptr(), k_scale.data_ptr(), km.data_ptr(),
+                                            v4, v_fp8.data_ptr(), sb, sh, sd, v_scale.data_ptr(), b, hq, hk, nq, nk,
+                                            n_stat, d, _dtype_code(q), per_thread, WARPQ, q_per_bh, k_per_bh,
+                                            float(scale_max), _stream(q)))
+    return q_int8, q_scale, k_int8, k_scale, km, v_fp8, v_scale
+
+
 def quant_q_int8(q, qk_quant_gran="per_thread", WARPQ=32, BLKQ=128, tensor_layout="HND"):
     """The Q half of per_warp_int8 / per_thread_int8 alone."""
     _require_cuda(q)

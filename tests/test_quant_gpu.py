@@ -193,3 +193,30 @@ def test_single_launch_qk_prologue_equals_separate_calls(dtype, layout, gran, wa
     assert torch.equal(q8, q8r)
     nwritten = (nq + warpq - 1) // warpq if gran == "per_warp" else qs.size(-1)
     assert torch.equal(qs[..., :nwritten], qsr[..., :nwritten])
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("layout", ["HND", "NHD"])
+@pytest.mark.parametrize("gran", ["per_thread", "per_warp"])
+@pytest.mark.parametrize("scale_max", [448.0, 2.25])
+@pytest.mark.parametrize("nq,nk,d,hq,hk", [(4096, 4096, 128, 4, 4), (1000, 1500, 64, 4, 2), (77, 100, 128, 2, 2),
+                                           (130, 5003, 128, 6, 2)])
+def test_single_launch_qkv_prologue_equals_separate_calls(dtype, layout, gran, scale_max, nq, nk, d, hq, hk):
+    """sage_prepass_qkv_fp8 (K slices, V slices and Q tiles in one grid) = sage_prepass_qk_int8 +
+    sage_per_channel_fp8(smooth_v = 0), bit for bit, including the padded tail of v_fp8 and the caller-side
+    padding to 128 tokens (n_stat)."""
+    q = make(2, hq, nq, d, dtype, layout, 31)
+    k = make(2, hk, nk, d, dtype, layout, 32) + 0.5
+    v = make(2, hk, nk, d, dtype, layout, 33)
+    n_stat = (nk + 127) // 128 * 128
+    q8, qs, k8, ks, km, v8, vs = sb.prepass_qkv_fp8(q, k, v, gran, WARPQ=32, tensor_layout=layout,
+                                                    scale_max=scale_max, _n_stat=n_stat)
+    q8r, qsr, k8r, ksr, kmr = sb.prepass_qk_int8(q, k, gran, WARPQ=32, tensor_layout=layout)
+    v8r, vsr, _ = sb.per_channel_fp8(v, tensor_layout=layout, scale_max=scale_max, smooth_v=False, _n_stat=n_stat)
+    assert torch.equal(km, kmr)
+    assert torch.equal(k8, k8r) and torch.equal(ks, ksr)
+    assert torch.equal(q8, q8r)
+    nwritten = (nq + 31) // 32 if gran == "per_warp" else qs.size(-1)
+    assert torch.equal(qs[..., :nwritten], qsr[..., :nwritten])
+    assert torch.equal(vs, vsr)
+    assert v8.shape == v8r.shape and torch.equal(v8.view(torch.uint8), v8r.view(torch.uint8))
