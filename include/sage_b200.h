@@ -90,11 +90,14 @@ int sage_smooth_quant_k_int8(sage_tensor4 k, void* mean_out, sage_tensor4 out, f
  * (sage_quant_per_thread_int8(is_key = 0, tile = warp_q) if per_thread, else sage_quant_int8(block =
  * warp_q)) produce, bit for bit.  q: [B,Hq,Nq,D], k: [B,Hkv,Nk,D] (strides given); k_mean_out [B,Hkv,D].
  * q_scale: [B,Hq,q_scale_per_bh] (>= ceil(Nq/128)*(128/warp_q)*8 per_thread, >= ceil(Nq/warp_q) else),
- * k_scale: [B,Hkv,k_scale_per_bh] (>= ceil(Nk/64)*4 per_thread, >= ceil(Nk/64) else). */
+ * k_scale: [B,Hkv,k_scale_per_bh] (>= ceil(Nk/64)*4 per_thread, >= ceil(Nk/64) else).
+ * d_og (0 = D): real head_dim of q / k when it is not 64 or 128 (a multiple of 8, <= D): the input rows
+ * hold d_og elements, the codes and the mean are written D wide with zeros beyond d_og - the caller-side
+ * F.pad of core.py:590-601 without its three extra passes over q, k, v. */
 int sage_prepass_qk_int8(sage_tensor4 q, sage_tensor4 k, sage_tensor4 q_out, sage_tensor4 k_out,
                          float* q_scale, float* k_scale, void* k_mean_out, int B, int Hq, int Hkv, int Nq,
                          int Nk, int D, int dtype, int per_thread, int warp_q, int q_scale_per_bh,
-                         int k_scale_per_bh, void* stream);
+                         int k_scale_per_bh, int d_og, void* stream);
 
 /* The Q/K/V prologue of the fp8-P.V operator (no smooth_v) in one launch: what sage_prepass_qk_int8(q, k) and
  * sage_per_channel_fp8(v, smooth_v = 0) produce, bit for bit (same arguments; v is [B,Hkv,Nk,D], n_stat as for
@@ -104,7 +107,7 @@ int sage_prepass_qkv_fp8(sage_tensor4 q, sage_tensor4 k, sage_tensor4 q_out, sag
                          int64_t vo_stride_b, int64_t vo_stride_h, int64_t vo_stride_d, float* v_scale,
                          int B, int Hq, int Hkv, int Nq, int Nk, int n_stat, int D, int dtype,
                          int per_thread, int warp_q, int q_scale_per_bh, int k_scale_per_bh,
-                         float scale_max, void* stream);
+                         float scale_max, int d_og, void* stream);
 
 /* out(f16)[b,h,n,d] = half( x - mean ) in the input type's packed arithmetic. */
 int sage_sub_mean(sage_tensor4 x, const void* mean, sage_tensor4 out, int B, int H, int N, int D,
@@ -140,6 +143,8 @@ typedef struct sage_attn_args {
   int out_dtype;   /* SAGE_DTYPE_* */
   float sm_scale;
   void* debug_s;   /* NULL, or int32 [B,Hq,ceil256(Nq),128]: raw QK^T of kv tile 0 (test hook) */
+  int d_og;        /* 0 = D, else the real head_dim (multiple of 8, <= D) of o and of an f16 v: their rows hold
+                      d_og elements; TMA zero-fills / clips the columns up to D (no F.pad, no output slice) */
 } sage_attn_args;
 
 int sage_attn_i8_f16(const sage_attn_args* a, void* stream);

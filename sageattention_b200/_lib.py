@@ -28,7 +28,7 @@ class AttnArgs(ctypes.Structure):
         ("q_scale", c_vp), ("k_scale", c_vp), ("v_scale", c_vp), ("v_mean", c_vp), ("lse", c_vp),
         ("B", c_int), ("Hq", c_int), ("Hkv", c_int), ("Nq", c_int), ("Nk", c_int), ("D", c_int),
         ("npad_v", c_int), ("gran", c_int), ("warp_q", c_int), ("is_causal", c_int),
-        ("out_dtype", c_int), ("sm_scale", c_f32), ("debug_s", c_vp),
+        ("out_dtype", c_int), ("sm_scale", c_f32), ("debug_s", c_vp), ("d_og", c_int),
     ]
 
 
@@ -44,9 +44,9 @@ SIGNATURES = {
                                            c_int, c_int, c_vp]),
     "sage_smooth_quant_k_int8": (c_int, [Tensor4, c_vp, Tensor4, c_vp, c_int, c_int, c_int, c_int, c_int,
                                          c_int, c_int, c_vp]),
-    "sage_prepass_qk_int8": (c_int, [Tensor4, Tensor4, Tensor4, Tensor4, c_vp, c_vp, c_vp] + [c_int] * 11 + [c_vp]),
+    "sage_prepass_qk_int8": (c_int, [Tensor4, Tensor4, Tensor4, Tensor4, c_vp, c_vp, c_vp] + [c_int] * 12 + [c_vp]),
     "sage_prepass_qkv_fp8": (c_int, [Tensor4, Tensor4, Tensor4, Tensor4, c_vp, c_vp, c_vp, Tensor4, c_vp, c_i64, c_i64,
-                                     c_i64, c_vp] + [c_int] * 12 + [c_f32, c_vp]),
+                                     c_i64, c_vp] + [c_int] * 12 + [c_f32, c_int, c_vp]),
     "sage_sub_mean": (c_int, [Tensor4, c_vp, Tensor4, c_int, c_int, c_int, c_int, c_int, c_vp]),
     "sage_per_channel_fp8_workspace_bytes": (ctypes.c_size_t, [c_int] * 4),
     "sage_per_channel_fp8": (c_int, [Tensor4, c_vp, c_i64, c_i64, c_i64, c_vp, c_vp, c_int, c_int, c_int,

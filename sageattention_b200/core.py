@@ -59,7 +59,14 @@ def _lse_correction(q, km, tensor_layout):
     return torch.matmul(qh, kmq.unsqueeze(-1)).squeeze(-1).to(torch.float32)
 
 
-def _quantize_qk(q, k, smooth_k, qk_quant_gran, tensor_layout, warp_q, return_lse):
+def _fold_padding(head_dim, smooth_k, smooth_v):
+    """head_dim not 64 / 128: the sm_100a kernels can take the tensors as they are (multiples of 8, default
+    smooth_k path without smooth_v): the quantisers write codes of the padded width, TMA zero-fills V and clips
+    O.  Otherwise the reference's F.pad copies (core.py:590-601) are made."""
+    return head_dim not in (64, 128) and head_dim <= 128 and head_dim % 8 == 0 and smooth_k and not smooth_v
+
+
+def _quantize_qk(q, k, smooth_k, qk_quant_gran, tensor_layout, warp_q, return_lse, fold=False):
     """The quantisation prologue (core.py:611-632): Q codes, and for K either the fused
     mean + quantise launch (smooth_k) or the plain quantiser.  Returns the four quantiser outputs
     and the LSE correction (None unless smooth_k and return_lse)."""
@@ -68,8 +75,9 @@ def _quantize_qk(q, k, smooth_k, qk_quant_gran, tensor_layout, warp_q, return_ls
         # from HBM) and Q tiles side by side (measured at C2: per_thread 105 us against 41 + 72 us as
         # two launches, per_warp 89 us against 45 + 62 us)
         q_int8, q_scale, k_int8, k_scale, km = prepass_qk_int8(q, k, qk_quant_gran, WARPQ=warp_q,
-                                                                 tensor_layout=tensor_layout)
-        return q_int8, q_scale, k_int8, k_scale, (_lse_correction(q, km, tensor_layout) if return_lse else None)
+                                                                 tensor_layout=tensor_layout, _pad_head_dim=fold)
+        return q_int8, q_scale, k_int8, k_scale, (_lse_correction(q, km[..., :q.size(-1)], tensor_layout)
+                                                    if return_lse else None)
     if qk_quant_gran == "per_warp":
         out = per_warp_int8(q, k, None, tensor_layout=tensor_layout, BLKQ=128, WARPQ=warp_q, BLKK=64)
     else:
@@ -108,6 +116,7 @@ def _launch(fp8, q_int8, k_int8, v, o, q_scale, k_scale, v_scale, v_mean, tensor
     a.out_dtype = _dtype_code(o)
     a.sm_scale = float(sm_scale)
     a.debug_s = debug_s.data_ptr() if debug_s is not None else None
+    a.d_og = o.size(-1) if o.size(-1) != d else 0
     fn = lib.sage_attn_i8_f8 if fp8 else lib.sage_attn_i8_f16
     with torch.cuda.device(o.device):
         if KERNEL_EVENTS is not None:
@@ -159,17 +168,19 @@ def sageattn_qk_int8_pv_fp16_cuda(
         raise ValueError(f"Unsupported pv_accum_dtype: {pv_accum_dtype}")
     dtype = q.dtype
     head_dim_og = q.size(-1)
-    q, k, v = _pad_head_dim(q, k, v)
-    assert q.stride(-1) == 1 and k.stride(-1) == 1 and v.stride(-1) == 1, "Last dim of qkv must be contiguous."
-    if sm_scale is None:
-        sm_scale = head_dim_og ** -0.5
-    warp_q = 16 if (q.size(-1) == 128 and pv_accum_dtype == "fp16+fp32") else 32
-    q_int8, q_scale, k_int8, k_scale, lse_correction = _quantize_qk(q, k, smooth_k, qk_quant_gran, tensor_layout,
-                                                                    warp_q, return_lse)
-    o = torch.empty(q.size(), dtype=dtype, device=q.device)
     if pv_accum_dtype in ["fp32", "fp16+fp32"] and smooth_v:
         warnings.warn(f"pv_accum_dtype is {pv_accum_dtype}, smooth_v will be ignored.")
         smooth_v = False
+    fold = _fold_padding(head_dim_og, smooth_k, smooth_v)
+    if not fold:
+        q, k, v = _pad_head_dim(q, k, v)
+    assert q.stride(-1) == 1 and k.stride(-1) == 1 and v.stride(-1) == 1, "Last dim of qkv must be contiguous."
+    if sm_scale is None:
+        sm_scale = head_dim_og ** -0.5
+    warp_q = 16 if (head_dim_og > 64 and pv_accum_dtype == "fp16+fp32") else 32
+    q_int8, q_scale, k_int8, k_scale, lse_correction = _quantize_qk(q, k, smooth_k, qk_quant_gran, tensor_layout,
+                                                                    warp_q, return_lse, fold)
+    o = torch.empty(q.size(), dtype=dtype, device=q.device)
     v_mean = None
     if smooth_v:
         v16, vm = sub_mean(v, tensor_layout=tensor_layout)
@@ -208,17 +219,19 @@ def sageattn_qk_int8_pv_fp8_cuda(
         raise ValueError(f"Unsupported pv_accum_dtype: {pv_accum_dtype}")
     dtype = q.dtype
     head_dim_og = q.size(-1)
-    q, k, v = _pad_head_dim(q, k, v)
-    assert q.stride(-1) == 1 and k.stride(-1) == 1 and v.stride(-1) == 1, "Last dim of qkv must be contiguous."
-    if sm_scale is None:
-        sm_scale = head_dim_og ** -0.5
-    o = torch.empty(q.size(), dtype=dtype, device=q.device)
     if pv_accum_dtype == "fp32+fp32" and smooth_v:
         warnings.warn("pv_accum_dtype is 'fp32+fp32', smooth_v will be ignored.")
         smooth_v = False
     if pv_accum_dtype == "fp32+fp16" and smooth_v:
         warnings.warn("pv_accum_dtype is 'fp32+fp16', smooth_v will be ignored.")
         smooth_v = False
+    fold = _fold_padding(head_dim_og, smooth_k, smooth_v) and k.shape == v.shape
+    if not fold:
+        q, k, v = _pad_head_dim(q, k, v)
+    assert q.stride(-1) == 1 and k.stride(-1) == 1 and v.stride(-1) == 1, "Last dim of qkv must be contiguous."
+    if sm_scale is None:
+        sm_scale = head_dim_og ** -0.5
+    o = torch.empty(q.size(), dtype=dtype, device=q.device)
     quant_v_scale_max = 2.25 if pv_accum_dtype == "fp32+fp16" else 448.0
     kv_len = k.size(2) if tensor_layout == "HND" else k.size(1)
     # the reference zero-pads V to a multiple of 128 tokens first (core.py:822-828); the kernels
@@ -228,8 +241,9 @@ def sageattn_qk_int8_pv_fp8_cuda(
         # the whole prologue in ONE launch: K slices (mean + quantise), V slices (range + e4m3 transpose) and
         # Q tiles side by side (bit-identical to the separate launches; measured at C2 in DESIGN 3.2)
         q_int8, q_scale, k_int8, k_scale, km, v_fp8, v_scale = prepass_qkv_fp8(
-            q, k, v, qk_quant_gran, WARPQ=32, tensor_layout=tensor_layout, scale_max=quant_v_scale_max, _n_stat=n_stat)
-        lse_correction = _lse_correction(q, km, tensor_layout) if return_lse else None
+            q, k, v, qk_quant_gran, WARPQ=32, tensor_layout=tensor_layout, scale_max=quant_v_scale_max, _n_stat=n_stat,
+            _pad_head_dim=fold)
+        lse_correction = _lse_correction(q, km[..., :q.size(-1)], tensor_layout) if return_lse else None
         vm = None
     else:
         q_int8, q_scale, k_int8, k_scale, lse_correction = _quantize_qk(q, k, smooth_k, qk_quant_gran, tensor_layout,

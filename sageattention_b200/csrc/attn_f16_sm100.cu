@@ -840,6 +840,9 @@ template <int D, bool kFp8>
 static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
   using L = SmemLayout<D, kFp8>;
   CUtensorMap tmQ, tmK, tmV, tmO;
+  // real head_dim of o (and of an f16 v): columns [d_og, D) are zero-filled on load and clipped on store
+  const int d_og = a->d_og > 0 ? a->d_og : D;
+  SAGE_REQUIRE(d_og <= D && d_og % 8 == 0, "d_og (%d) must be a multiple of 8 and <= head_dim %d", d_og, D);
   const CUtensorMapSwizzle qk_swz = (D == 128) ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B;
   int rc;
   rc = make_map4(&tmQ, CU_TENSOR_MAP_DATA_TYPE_UINT8, a->q8.ptr, D, a->Nq, a->Hq, a->B,
@@ -855,13 +858,13 @@ static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
                    a->v.stride_n, a->v.stride_h, a->v.stride_b, kTileKV, D,
                    CU_TENSOR_MAP_SWIZZLE_128B, "v_fp8");
   } else {
-    rc = make_map4(&tmV, CU_TENSOR_MAP_DATA_TYPE_UINT16, a->v.ptr, D, a->Nk, a->Hkv, a->B,
+    rc = make_map4(&tmV, CU_TENSOR_MAP_DATA_TYPE_UINT16, a->v.ptr, d_og, a->Nk, a->Hkv, a->B,
                    a->v.stride_n * 2, a->v.stride_h * 2, a->v.stride_b * 2, 64, kTileKV,
                    CU_TENSOR_MAP_SWIZZLE_128B, "v_f16");
   }
   if (rc) return rc;
   // o rows through TMA: 64-column (128 B) blocks of 128 rows; rows >= Nq are clipped by the hardware
-  rc = make_map4(&tmO, CU_TENSOR_MAP_DATA_TYPE_UINT16, a->o.ptr, D, a->Nq, a->Hq, a->B,
+  rc = make_map4(&tmO, CU_TENSOR_MAP_DATA_TYPE_UINT16, a->o.ptr, d_og, a->Nq, a->Hq, a->B,
                  a->o.stride_n * 2, a->o.stride_h * 2, a->o.stride_b * 2, 64, kTileQ,
                  CU_TENSOR_MAP_SWIZZLE_128B, "o");
   if (rc) return rc;

@@ -162,17 +162,27 @@ def smooth_quant_k_int8(k, qk_quant_gran="per_thread", tensor_layout="HND"):
     return k_int8, k_scale, km
 
 
-def prepass_qk_int8(q, k, qk_quant_gran="per_thread", WARPQ=32, tensor_layout="HND"):
+def _padded_head_dim(d: int) -> int:
+    """64 / 128 as core.py:590-601 pads to; raises for head_dim > 128."""
+    if d > 128:
+        raise ValueError(f"Unsupported head_dim: {d}")
+    return 64 if d <= 64 else 128
+
+
+def prepass_qk_int8(q, k, qk_quant_gran="per_thread", WARPQ=32, tensor_layout="HND", _pad_head_dim=False):
     """The operator's Q/K prologue with smooth_k in ONE launch (core.py:611-632): km = k.mean(seq),
     K codes/scales for that mean and Q codes/scales.  Returns (q_int8, q_scale, k_int8, k_scale, km),
     identical to quant_q_int8(q) + smooth_quant_k_int8(k)."""
     _require_cuda(q, k)
     lib = _lib.load()
-    b, hq, nq, d, q4 = _dims(q, tensor_layout)
+    b, hq, nq, d_og, q4 = _dims(q, tensor_layout)
     _, hk, nk, _, k4 = _dims(k, tensor_layout)
+    # `_pad_head_dim` (internal): head_dim is a multiple of 8 but not 64 / 128 - the kernel reads the rows as
+    # they are and writes codes / mean of the padded width (zeros beyond head_dim), instead of three F.pad copies
+    d = _padded_head_dim(d_og) if _pad_head_dim else d_og
     per_thread = 1 if qk_quant_gran == "per_thread" else 0
-    q_int8 = torch.empty(q.shape, dtype=torch.int8, device=q.device)
-    k_int8 = torch.empty(k.shape, dtype=torch.int8, device=k.device)
+    q_int8 = torch.empty(q.shape[:-1] + (d,), dtype=torch.int8, device=q.device)
+    k_int8 = torch.empty(k.shape[:-1] + (d,), dtype=torch.int8, device=k.device)
     _, _, _, _, qo4 = _dims(q_int8, tensor_layout)
     _, _, _, _, ko4 = _dims(k_int8, tensor_layout)
     q_per_bh = (nq + 127) // 128 * (128 // WARPQ) * (8 if per_thread else 1)
@@ -185,25 +195,26 @@ def prepass_qk_int8(q, k, qk_quant_gran="per_thread", WARPQ=32, tensor_layout="H
     with torch.cuda.device(q.device):
         _lib.check(lib.sage_prepass_qk_int8(q4, k4, qo4, ko4, q_scale.data_ptr(), k_scale.data_ptr(), km.data_ptr(),
                                             b, hq, hk, nq, nk, d, _dtype_code(q), per_thread, WARPQ, q_per_bh,
-                                            k_per_bh, _stream(q)))
+                                            k_per_bh, d_og, _stream(q)))
     return q_int8, q_scale, k_int8, k_scale, km
 
 
 def prepass_qkv_fp8(q, k, v, qk_quant_gran="per_thread", WARPQ=32, tensor_layout="HND", scale_max=448.0,
-                    _n_stat=None):
+                    _n_stat=None, _pad_head_dim=False):
     """The fp8-P.V operator's whole prologue (smooth_k, no smooth_v) in ONE launch.  Returns
     (q_int8, q_scale, k_int8, k_scale, km, v_fp8, v_scale), identical to prepass_qk_int8(q, k) +
     per_channel_fp8(v, smooth_v=False): K slices, V slices and Q tiles run side by side in one grid."""
     _require_cuda(q, k, v)
     lib = _lib.load()
-    b, hq, nq, d, q4 = _dims(q, tensor_layout)
+    b, hq, nq, d_og, q4 = _dims(q, tensor_layout)
     _, hk, nk, _, k4 = _dims(k, tensor_layout)
     _, hv, nv, _, v4 = _dims(v, tensor_layout)
     if (hv, nv) != (hk, nk):
         raise ValueError("k and v must have the same heads and length")
+    d = _padded_head_dim(d_og) if _pad_head_dim else d_og   # see prepass_qk_int8
     per_thread = 1 if qk_quant_gran == "per_thread" else 0
-    q_int8 = torch.empty(q.shape, dtype=torch.int8, device=q.device)
-    k_int8 = torch.empty(k.shape, dtype=torch.int8, device=k.device)
+    q_int8 = torch.empty(q.shape[:-1] + (d,), dtype=torch.int8, device=q.device)
+    k_int8 = torch.empty(k.shape[:-1] + (d,), dtype=torch.int8, device=k.device)
     _, _, _, _, qo4 = _dims(q_int8, tensor_layout)
     _, _, _, _, ko4 = _dims(k_int8, tensor_layout)
     q_per_bh = (nq + 127) // 128 * (128 // WARPQ) * (8 if per_thread else 1)
@@ -225,7 +236,7 @@ def prepass_qkv_fp8(q, k, v, qk_quant_gran="per_thread", WARPQ=32, tensor_layout
         _lib.check(lib.sage_prepass_qkv_fp8(q4, k4, qo4, ko4, q_scale.data_ptr(), k_scale.data_ptr(), km.data_ptr(),
                                             v4, v_fp8.data_ptr(), sb, sh, sd, v_scale.data_ptr(), b, hq, hk, nq, nk,
                                             n_stat, d, _dtype_code(q), per_thread, WARPQ, q_per_bh, k_per_bh,
-                                            float(scale_max), _stream(q)))
+                                            float(scale_max), d_og, _stream(q)))
     return q_int8, q_scale, k_int8, k_scale, km, v_fp8, v_scale
 
 

@@ -276,3 +276,35 @@ def test_kernel_in_cuda_graph(pv):
         g.replay()
         torch.cuda.synchronize()
         assert torch.equal(o, o_ref)
+
+
+@pytest.mark.parametrize("fn", ["sageattn", "sageattn_qk_int8_pv_fp16_cuda", "sageattn_qk_int8_pv_fp8_cuda"])
+@pytest.mark.parametrize("layout", ["HND", "NHD"])
+@pytest.mark.parametrize("d_og,dtype", [(40, torch.float16), (72, torch.bfloat16), (96, torch.float16), (112, torch.bfloat16)])
+def test_head_dim_padding_inside_the_kernels(fn, layout, d_og, dtype):
+    """head_dim not in {64, 128}: the reference zero-pads q, k, v with three F.pad copies and
+    slices the output (core.py:590-601, 648).  Here the quantisers read the rows as they are and write codes of
+    the padded width, TMA zero-fills V and clips O.  The output must be BIT-identical to the same operator run on
+    explicitly padded copies."""
+    b, hq, hk, n = 2, 4, 2, 777
+    causal = d_og in (40, 96)
+    q, k, v = make_qkv(b, hq, hk, n, n, d_og, dtype, seed=d_og)
+    if layout == "NHD":
+        q, k, v = (t.transpose(1, 2).contiguous() for t in (q, k, v))
+    f = getattr(sb, fn)
+    o, lse = f(q, k, v, tensor_layout=layout, is_causal=causal, return_lse=True)
+    pad = (64 if d_og <= 64 else 128) - d_og
+    qp, kp, vp = (torch.nn.functional.pad(t, (0, pad)) for t in (q, k, v))
+    op, lsep = f(qp, kp, vp, tensor_layout=layout, is_causal=causal, sm_scale=d_og ** -0.5, return_lse=True)
+    torch.cuda.synchronize()
+    assert o.shape == q.shape and o.is_contiguous()
+    assert torch.equal(o, op[..., :d_og])
+    # the LSE adds torch.matmul(q, km) (core.py:613-617), whose reduction order differs between a d_og- and a
+    # D-column operand and whose result torch rounds to the 16-bit input type: equal up to that rounding
+    assert torch.allclose(lse, lsep, rtol=0, atol=3e-2)
+    # and it is still attention: fp32 SDPA on the unpadded inputs
+    qh, kh, vh = ((t if layout == "HND" else t.transpose(1, 2)).float() for t in (q, k, v))
+    ref = torch.nn.functional.scaled_dot_product_attention(qh, kh.repeat_interleave(hq // hk, 1),
+                                                           vh.repeat_interleave(hq // hk, 1), is_causal=causal)
+    cos, _, _ = accuracy(o if layout == "HND" else o.transpose(1, 2), ref)
+    assert cos >= 0.999, cos
