@@ -14,7 +14,7 @@ from typing import Any, Optional
 import torch
 
 from . import _lib
-from .quant import (_dims, _dtype_code, _require_cuda, _stream, per_block_int8, per_channel_fp8, per_thread_int8,
+from .quant import (_dims, _dtype_code, _on_device, _require_cuda, _stream, per_block_int8, per_channel_fp8, per_thread_int8,
                     per_warp_int8, prepass_qk_int8, prepass_qkv_fp8, quant_q_int8, seq_mean, smooth_quant_k_int8,
                     sub_mean)
 
@@ -118,7 +118,7 @@ def _launch(fp8, q_int8, k_int8, v, o, q_scale, k_scale, v_scale, v_mean, tensor
     a.debug_s = debug_s.data_ptr() if debug_s is not None else None
     a.d_og = o.size(-1) if o.size(-1) != d else 0
     fn = lib.sage_attn_i8_f8 if fp8 else lib.sage_attn_i8_f16
-    with torch.cuda.device(o.device):
+    with _on_device(o.device):
         if KERNEL_EVENTS is not None:
             e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             e0.record()

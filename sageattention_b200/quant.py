@@ -42,7 +42,29 @@ def _dims(t: torch.Tensor, tensor_layout: str):
 
 
 def _stream(t: torch.Tensor):
-    return torch.cuda.current_stream(t.device).cuda_stream
+    # raw handle of torch's current stream on the tensor's device (the Stream object costs ~5 us to build)
+    return torch._C._cuda_getCurrentRawStream(t.device.index)
+
+
+class _on_device:
+    """`with torch.cuda.device(dev)` that costs nothing when `dev` already is the current device (the usual
+    case; the context manager itself is ~5 us per call)."""
+    __slots__ = ("idx", "prev")
+
+    def __init__(self, dev: torch.device):
+        self.idx = dev.index
+        self.prev = -1
+
+    def __enter__(self):
+        cur = torch._C._cuda_getDevice()
+        if cur != self.idx:
+            self.prev = cur
+            torch._C._cuda_setDevice(self.idx)
+
+    def __exit__(self, *exc):
+        if self.prev >= 0:
+            torch._C._cuda_setDevice(self.prev)
+        return False
 
 
 def _require_cuda(*ts):
@@ -69,7 +91,7 @@ def seq_mean(x: torch.Tensor, tensor_layout: str = "HND") -> torch.Tensor:
     b, h, n, d, x4 = _dims(x, tensor_layout)
     out = torch.empty((b, h, d), dtype=x.dtype, device=x.device)
     ws = torch.empty(lib.sage_seq_mean_workspace_bytes(b, h, n, d), dtype=torch.uint8, device=x.device)
-    with torch.cuda.device(x.device):
+    with _on_device(x.device):
         _lib.check(lib.sage_seq_mean(x4, out.data_ptr(), b, h, n, d, _dtype_code(x), ws.data_ptr(), _stream(x)))
     return out
 
@@ -87,7 +109,7 @@ def _quant_block(x, km, block, sm_scale, tensor_layout, scale_per_bh=None):
     scale = (torch.empty if scale_per_bh == nblk else torch.zeros)(
         (b, h, scale_per_bh), dtype=torch.float32, device=x.device)
     km_c, km_ptr = _mean_ptr(km, b, h, d, x)
-    with torch.cuda.device(x.device):
+    with _on_device(x.device):
         _lib.check(lib.sage_quant_int8(x4, km_ptr, o4, scale.data_ptr(), b, h, n, d, _dtype_code(x), block,
                                        scale_per_bh, 0 if sm_scale is None else 1,
                                        0.0 if sm_scale is None else float(sm_scale), _stream(x)))
@@ -135,7 +157,7 @@ def per_thread_int8(q, k, km=None, BLKQ=128, WARPQ=32, BLKK=64, WARPK=64, sm_sca
     q_scale = torch.empty((b, hq, (nq + BLKQ - 1) // BLKQ * (BLKQ // WARPQ) * 8), dtype=torch.float32, device=q.device)
     k_scale = torch.empty((b, hk, (nk + BLKK - 1) // BLKK * (BLKK // WARPK) * 4), dtype=torch.float32, device=q.device)
     km_c, km_ptr = _mean_ptr(km, b, hk, d, k)
-    with torch.cuda.device(q.device):
+    with _on_device(q.device):
         _lib.check(lib.sage_quant_per_thread_int8(q4, None, qo4, q_scale.data_ptr(), b, hq, nq, d, _dtype_code(q),
                                                   0, WARPQ, _stream(q)))
         _lib.check(lib.sage_quant_per_thread_int8(k4, km_ptr, ko4, k_scale.data_ptr(), b, hk, nk, d, _dtype_code(k),
@@ -156,7 +178,7 @@ def smooth_quant_k_int8(k, qk_quant_gran="per_thread", tensor_layout="HND"):
     per_bh = (n + 63) // 64 * (4 if per_thread else 1)
     k_scale = torch.empty((b, h, per_bh), dtype=torch.float32, device=k.device)
     km = torch.empty((b, h, d), dtype=k.dtype, device=k.device)
-    with torch.cuda.device(k.device):
+    with _on_device(k.device):
         _lib.check(lib.sage_smooth_quant_k_int8(k4, km.data_ptr(), ko4, k_scale.data_ptr(), b, h, n, d,
                                                 _dtype_code(k), per_thread, per_bh, _stream(k)))
     return k_int8, k_scale, km
@@ -192,7 +214,7 @@ def prepass_qk_int8(q, k, qk_quant_gran="per_thread", WARPQ=32, tensor_layout="H
         (b, hq, q_per_bh), dtype=torch.float32, device=q.device)
     k_scale = torch.empty((b, hk, k_per_bh), dtype=torch.float32, device=q.device)
     km = torch.empty((b, hk, d), dtype=k.dtype, device=k.device)
-    with torch.cuda.device(q.device):
+    with _on_device(q.device):
         _lib.check(lib.sage_prepass_qk_int8(q4, k4, qo4, ko4, q_scale.data_ptr(), k_scale.data_ptr(), km.data_ptr(),
                                             b, hq, hk, nq, nk, d, _dtype_code(q), per_thread, WARPQ, q_per_bh,
                                             k_per_bh, d_og, _stream(q)))
@@ -232,7 +254,7 @@ def prepass_qkv_fp8(q, k, v, qk_quant_gran="per_thread", WARPQ=32, tensor_layout
         v_fp8 = torch.empty((b, d, hk, npad), dtype=torch.float8_e4m3fn, device=v.device)
         sb, sh, sd = v_fp8.stride(0), v_fp8.stride(2), v_fp8.stride(1)
     v_scale = torch.empty((b, hk, d), dtype=torch.float32, device=v.device)
-    with torch.cuda.device(q.device):
+    with _on_device(q.device):
         _lib.check(lib.sage_prepass_qkv_fp8(q4, k4, qo4, ko4, q_scale.data_ptr(), k_scale.data_ptr(), km.data_ptr(),
                                             v4, v_fp8.data_ptr(), sb, sh, sd, v_scale.data_ptr(), b, hq, hk, nq, nk,
                                             n_stat, d, _dtype_code(q), per_thread, WARPQ, q_per_bh, k_per_bh,
@@ -251,7 +273,7 @@ def quant_q_int8(q, qk_quant_gran="per_thread", WARPQ=32, BLKQ=128, tensor_layou
     q_int8 = torch.empty(q.shape, dtype=torch.int8, device=q.device)
     _, _, _, _, qo4 = _dims(q_int8, tensor_layout)
     q_scale = torch.empty((b, hq, (nq + BLKQ - 1) // BLKQ * (BLKQ // WARPQ) * 8), dtype=torch.float32, device=q.device)
-    with torch.cuda.device(q.device):
+    with _on_device(q.device):
         _lib.check(lib.sage_quant_per_thread_int8(q4, None, qo4, q_scale.data_ptr(), b, hq, nq, d, _dtype_code(q),
                                                   0, WARPQ, _stream(q)))
     return q_int8, q_scale
@@ -268,7 +290,7 @@ def sub_mean(v, tensor_layout="HND", vm=None):
     vm = vm.reshape(b, h, d).contiguous()
     out = torch.empty(v.shape, dtype=torch.float16, device=v.device)
     _, _, _, _, o4 = _dims(out, tensor_layout)
-    with torch.cuda.device(v.device):
+    with _on_device(v.device):
         _lib.check(lib.sage_sub_mean(v4, vm.data_ptr(), o4, b, h, n, d, _dtype_code(v), _stream(v)))
     return out, vm
 
@@ -294,7 +316,7 @@ def per_channel_fp8(v, tensor_layout="HND", scale_max=448.0, smooth_v=True, _n_s
     v_scale = torch.empty((b, h, d), dtype=torch.float32, device=v.device)
     vm = torch.empty((b, h, d), dtype=torch.float32, device=v.device) if smooth_v else None
     ws = torch.empty(lib.sage_per_channel_fp8_workspace_bytes(b, h, n, d), dtype=torch.uint8, device=v.device)
-    with torch.cuda.device(v.device):
+    with _on_device(v.device):
         _lib.check(lib.sage_per_channel_fp8(v4, v_fp8.data_ptr(), sb, sh, sd, v_scale.data_ptr(),
                                             vm.data_ptr() if smooth_v else None, b, h, n, n_stat, d,
                                             _dtype_code(v), float(scale_max), 1 if smooth_v else 0,
