@@ -308,3 +308,37 @@ def test_head_dim_padding_inside_the_kernels(fn, layout, d_og, dtype):
                                                            vh.repeat_interleave(hq // hk, 1), is_causal=causal)
     cos, _, _ = accuracy(o if layout == "HND" else o.transpose(1, 2), ref)
     assert cos >= 0.999, cos
+
+
+@pytest.mark.parametrize("pv", ["f8", "f16"])
+@pytest.mark.parametrize("d", [128, 64])
+def test_long_sequence_size_independent_properties(pv, d):
+    """At a length the CPU oracle cannot check (N = 20 040: 157 kv steps, 79 q pairs per head, ragged tail),
+    two exact properties of the kernels: (1) causal prefix - the first 1024 output rows depend only on the
+    first 1024 rows of q, k, v and go through the same tiles in the same order as a launch on that prefix
+    alone, so they must be BIT-identical to it; (2) scaling V by 2 (exact in f16 / e4m3 and in the fp32
+    accumulators) doubles every output exactly."""
+    b, h, n, pre = 1, 3, 20040, 1024
+    q8, qs, k8, ks, v, vs = _random_codes(b, h, h, n, n, d, pv, seed=77 + d)
+    sm = d ** -0.5
+    o = run_kernel(pv, q8, qs, k8, ks, v, vs, None, 3, True, sm, torch.float16)
+    assert torch.isfinite(o.float()).all()
+    # (1) prefix
+    cut = lambda t, m: t[:, :, :m].contiguous()
+    if pv == "f8":
+        v_pre = v[..., :pre].contiguous()
+    else:
+        v_pre = cut(v, pre)
+    o_pre = run_kernel(pv, cut(q8, pre), cut(qs, pre // 128 * 32), cut(k8, pre), cut(ks, pre // 64 * 4), v_pre, vs,
+                       None, 3, True, sm, torch.float16)
+    assert torch.equal(o[:, :, :pre], o_pre)
+    # (2) linearity in V (non-causal, so every kv step of every row takes part); bf16 output: averages over
+    # 20 K random values come close to zero, where an f16 output goes subnormal and doubling is no longer exact
+    o1 = run_kernel(pv, q8, qs, k8, ks, v, vs, None, 3, False, sm, torch.bfloat16)
+    if pv == "f8":
+        v2, vs2 = v, vs * 2.0            # the e4m3 codes stay, their per-channel scale doubles
+    else:
+        v2, vs2 = v * 2.0, None
+    o2 = run_kernel(pv, q8, qs, k8, ks, v2, vs2, None, 3, False, sm, torch.bfloat16)
+    torch.cuda.synchronize()
+    assert torch.equal(o2.float(), o1.float() * 2.0)
