@@ -198,6 +198,8 @@ def main():
                     help="DiT workloads under torchrun: head sharding (no collective) or Ulysses all-to-all")
     ap.add_argument("--sp-chunks", type=int, default=1,
                     help="Ulysses: groups of heads whose all-to-alls overlap the attention of another group")
+    ap.add_argument("--sp-transport", default="nccl", choices=["nccl", "p2p"],
+                    help="Ulysses: NCCL all-to-all, or copy-engine pushes into the peers' symmetric memory")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)
@@ -239,6 +241,7 @@ def main():
         base_fn = fn
         fn = lambda q_, k_, v_, is_causal=False: parallel.ulysses_sageattn(q_, k_, v_, attn_fn=base_fn,
                                                                            head_chunks=args.sp_chunks,
+                                                                           transport=args.sp_transport,
                                                                            is_causal=is_causal)
         n = n_loc * world
     else:
@@ -333,7 +336,7 @@ def main():
         "ms_per_step": t_ms, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
         "dtype": "int8+fp8" if fp8 else "int8+fp16", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {api} B={b} H={h} N={n} D={d} causal={causal} {dtype_name}, "
-                               f"heads per rank {h_loc}" + (f", Ulysses all-to-all (NCCL), {args.sp_chunks} head group(s) pipelined" if ulysses else ""),
+                               f"heads per rank {h_loc}" + (f", Ulysses all-to-all ({args.sp_transport}), {args.sp_chunks} head group(s) pipelined" if ulysses else ""),
                    "l2": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2" % (4 * nbytes / 1e6)},
         "e2e": {"value": e2e_val, "unit": "TOPS", "h2d_bytes_per_step": 3 * nbytes * world,
                 "d2h_bytes_per_step": nbytes * world, "ms_per_step": e2e_ms},

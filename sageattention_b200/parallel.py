@@ -134,12 +134,119 @@ def _ulysses_b1(q, k, v, group, world, attn_fn, head_chunks, kwargs):
     return out
 
 
+# ---------------------------------------------------------------------------------------------------
+# Batch-1 Ulysses over NVLink peer memory (no NCCL kernel on the data path).  NCCL's all-to-all runs on SMs,
+# and the persistent attention grid holds all of them, so NCCL transfers cannot overlap the attention of
+# another head group.  Here every rank owns a symmetric-memory arena (torch.distributed._symmetric_memory:
+# CUDA IPC / fabric handles exchanged once); a rank PUSHES its head-group chunks straight into the peers'
+# arenas with contiguous device-to-device copies, which the copy engines execute - no SM needed - and a
+# signal-pad barrier tells the receivers that everything has landed.
+_ARENAS = {}
+
+
+def _arena(nbytes: int, device: torch.device, group):
+    """(handle, capacity) of this rank's symmetric arena of at least `nbytes` (same on every rank: the size
+    is a function of the call's shapes, so all ranks re-allocate together)."""
+    import torch.distributed._symmetric_memory as symm
+    key = (device.index, group.group_name)
+    cur = _ARENAS.get(key)
+    if cur is None or cur[1] < nbytes:
+        cap = max(nbytes, 1 << 20)
+        buf = symm.empty(cap, dtype=torch.uint8, device=device)
+        cur = (symm.rendezvous(buf, group), cap, buf)
+        _ARENAS[key] = cur
+    return cur[0], cur[1]
+
+
+def _ulysses_b1_p2p(q, k, v, group, world, attn_fn, head_chunks, kwargs):
+    rank = dist.get_rank(group)
+    n, h, d = q.shape[1:]
+    hk = k.size(2)
+    hp, hkp = h // world, hk // world
+    g = h // hk
+    es = q.element_size()
+    chunks = max(1, min(head_chunks, hkp))
+    bounds = [(hkp * c) // chunks for c in range(chunks + 1)]
+    # arena layout (bytes), identical on every rank: per chunk [q | k | v | o_back], each [P (source rank), n, heads, d]
+    offs, total = [], 0
+    for c in range(chunks):
+        hc_k = bounds[c + 1] - bounds[c]
+        sizes = [world * n * hc_k * g * d * es, world * n * hc_k * d * es, world * n * hc_k * d * es,
+                 world * n * hc_k * g * d * es]
+        o4 = []
+        for sz in sizes:
+            o4.append(total)
+            total += (sz + 255) // 256 * 256
+        offs.append(o4)
+    hdl, _ = _arena(total, q.device, group)
+    dt = q.dtype
+
+    def peer(p, byte_off, heads):  # rank p's slot for the rows this rank sends: [n, heads, d]
+        return hdl.get_buffer(p, (n, heads, d), dt, (byte_off + rank * n * heads * d * es) // es)
+
+    def mine(byte_off, heads):     # this rank's whole buffer: [P, n, heads, d]
+        return hdl.get_buffer(rank, (world, n, heads, d), dt, byte_off // es)
+
+    cur = torch.cuda.current_stream(q.device)
+    comm = _COMM_STREAMS.get(q.device)
+    if comm is None:
+        comm = _COMM_STREAMS[q.device] = torch.cuda.Stream(q.device)
+    comm.wait_stream(cur)
+    arrived = []
+    with torch.cuda.stream(comm):
+        hdl.barrier()  # every rank has finished reading its arena in the previous call
+        for c in range(chunks):
+            lo, hi = bounds[c], bounds[c + 1]
+            for x, a, b_, off in ((q, lo * g, hi * g, offs[c][0]), (k, lo, hi, offs[c][1]), (v, lo, hi, offs[c][2])):
+                hpx = x.size(2) // world
+                send = torch.empty((world, n, b_ - a, d), dtype=dt, device=x.device)
+                send.copy_(x.view(n, world, hpx, d)[:, :, a:b_].transpose(0, 1))   # the one gather copy (local)
+                for p in range(world):
+                    peer(p, off, b_ - a).copy_(send[p])                           # contiguous: copy engine, NVLink
+            hdl.barrier()  # all pushes of this head group have landed everywhere
+            ev = torch.cuda.Event()
+            ev.record(comm)
+            arrived.append(ev)
+    out = torch.empty((1, n, h, d), dtype=dt, device=q.device)
+    ov = out.view(n, world, hp, d)
+    back = []
+    for c in range(chunks):
+        lo, hi = bounds[c], bounds[c + 1]
+        cur.wait_event(arrived[c])
+        qh = mine(offs[c][0], (hi - lo) * g).view(1, world * n, (hi - lo) * g, d)
+        kh = mine(offs[c][1], hi - lo).view(1, world * n, hi - lo, d)
+        vh = mine(offs[c][2], hi - lo).view(1, world * n, hi - lo, d)
+        o = attn_fn(qh, kh, vh, tensor_layout="NHD", **kwargs).contiguous()
+        done = torch.cuda.Event()
+        done.record(cur)
+        o.record_stream(comm)
+        with torch.cuda.stream(comm):
+            comm.wait_event(done)
+            ob = o.view(world, n, (hi - lo) * g, d)   # chunk p = sequence block p: goes to rank p
+            for p in range(world):
+                peer(p, offs[c][3], (hi - lo) * g).copy_(ob[p])
+            hdl.barrier()
+            ev = torch.cuda.Event()
+            ev.record(comm)
+            back.append(ev)
+    for c in range(chunks):
+        lo, hi = bounds[c], bounds[c + 1]
+        cur.wait_event(back[c])
+        ov[:, :, lo * g:hi * g].copy_(mine(offs[c][3], (hi - lo) * g).transpose(0, 1))
+    comm.wait_stream(cur)  # the arena is read by `cur` until here; the next call's first barrier follows on comm
+    return out
+
+
 def ulysses_sageattn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, group=None,
-                     attn_fn: Optional[Callable] = None, head_chunks: int = 1, **kwargs) -> torch.Tensor:
+                     attn_fn: Optional[Callable] = None, head_chunks: int = 1, transport: str = "nccl",
+                     **kwargs) -> torch.Tensor:
     """Sequence-parallel attention.  q, k, v: this rank's sequence block, "NHD" layout
     [B, N/P, H, D] (all ranks hold equally long blocks; pad the sequence to a multiple of P first).
     Returns this rank's block of the output, [B, N/P, H, D].  kwargs go to the attention function
     (default: sageattn); `tensor_layout` is fixed to "NHD" and `return_lse` is not supported here.
+    `transport`: "nccl" (all_to_all_single) or, with B = 1 on GPUs of one node, "p2p": chunks are pushed into
+    the peers' symmetric-memory arenas by the copy engines, which (unlike NCCL's kernels) run under the
+    persistent attention grid of another head group.
     `head_chunks`: with B = 1, how many groups the rank's heads are split into so that the all-to-alls of
     one group overlap the attention of another (1 = no overlap)."""
     if kwargs.pop("return_lse", False):
@@ -155,6 +262,11 @@ def ulysses_sageattn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, group=No
         raise ValueError(f"head counts ({h}, {k.size(2)}) must be divisible by the world size {world}")
     if q.size(0) == 1 and k.size(0) == 1 and all(t.is_contiguous() for t in (q, k, v)):
         # the DiT case (B = 1): communication pipelined against attention over groups of heads
+        if transport == "p2p":
+            if not q.is_cuda:
+                raise ValueError("transport='p2p' needs CUDA tensors")
+            return _ulysses_b1_p2p(q, k, v, group if group is not None else dist.group.WORLD, world, attn_fn,
+                                   head_chunks, kwargs)
         return _ulysses_b1(q, k, v, group, world, attn_fn, head_chunks, kwargs)
     if k.size(2) == h and k.shape == q.shape:
         qkv = _seq_to_head_shard(torch.stack((q, k, v)), group, world)  # one collective for all three

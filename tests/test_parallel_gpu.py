@@ -25,9 +25,11 @@ def _worker(rank, world, port, q_out):
         nl = n // world
         sl = slice(rank * nl, (rank + 1) * nl)
         same = True
-        for chunks in (1, 2, 4):   # head groups pipelined against the all-to-alls: same bits every way
+        # head groups pipelined against the transfers, over NCCL or over peer memory: same bits every way,
+        # also when the same arena is used again by a second call
+        for transport, chunks in (("nccl", 1), ("nccl", 2), ("nccl", 4), ("p2p", 1), ("p2p", 2), ("p2p", 4), ("p2p", 2)):
             o = parallel.ulysses_sageattn(q[:, sl].contiguous(), k[:, sl].contiguous(), v[:, sl].contiguous(),
-                                          head_chunks=chunks)
+                                          head_chunks=chunks, transport=transport)
             torch.cuda.synchronize()
             same = same and torch.equal(o, full[:, sl])
         ref = torch.nn.functional.scaled_dot_product_attention(q.float().transpose(1, 2), k.float().transpose(1, 2),
