@@ -396,3 +396,33 @@ def sageattn_cpu_emulation(q, k, v, is_causal=False, sm_scale=None, smooth_k=Tru
         acc = acc * alpha[..., None] + torch.matmul(p.to(torch.float16).float(), v16[:, :, k0:k1])
         m = m_new
     return acc / l[..., None]
+
+
+def sageattn_varlen_ref(q, k, v, cu_seqlens_q, cu_seqlens_k, is_causal=False, sm_scale=None, smooth_k=True):
+    """CPU restatement of sageattn_varlen (sageattention/core.py:363-477): q [Tq, Hq, D], k / v [Tk, Hk, D]
+    packed along the token axis, cu_seqlens_* [batch + 1].
+
+    core.py:443-453 zero-pads head_dim to 64 / 128 (sm_scale keeps the original head_dim, :467-468);
+    :459-460 converts V to fp16; :462-464 smooths K with its mean over ALL tokens of the pack, in the input
+    dtype; triton/quant_per_block_varlen.py:60 quantises per block with the blocks restarting at every
+    sequence (Q blocks of 128 pre-scaled by sm_scale * log2 e, K blocks of 64); the Triton attention kernels
+    (attn_qk_int8_block_varlen.py:123, attn_qk_int8_per_block_causal_varlen.py:138) run the base-2 online
+    softmax per sequence with fp16 P and V and fp32 accumulation - i.e. `sageattn_cpu_emulation` per sequence.
+    Hq == Hk only (the emulation has no GQA broadcast); returns fp32 [Tq, Hq, D]."""
+    d = q.size(-1)
+    if sm_scale is None:
+        sm_scale = d ** -0.5
+    d_pad = 64 if d <= 64 else 128
+    if smooth_k:
+        k = k - k.mean(dim=0, keepdim=True)
+    outs = []
+    for i in range(len(cu_seqlens_q) - 1):
+        q0, q1 = int(cu_seqlens_q[i]), int(cu_seqlens_q[i + 1])
+        k0, k1 = int(cu_seqlens_k[i]), int(cu_seqlens_k[i + 1])
+        if q1 == q0:
+            continue
+        hnd = lambda t, a, b: torch.nn.functional.pad(t[a:b].float(), (0, d_pad - d)).transpose(0, 1).unsqueeze(0)
+        o = sageattn_cpu_emulation(hnd(q, q0, q1), hnd(k, k0, k1), hnd(v, k0, k1), is_causal=is_causal,
+                                   sm_scale=sm_scale, smooth_k=False)
+        outs.append(o[0, :, :, :d].transpose(0, 1))
+    return torch.cat(outs)

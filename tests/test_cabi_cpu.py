@@ -49,6 +49,12 @@ def test_argument_validation_without_gpu():
     a = _lib.AttnArgs()
     a.D = 96
     assert lib.sage_attn_i8_f8(ctypes.byref(a), None) < 0
+    # the real head_dim of the one-launch prologues must be a multiple of 8 and <= the padded one
+    rc = lib.sage_prepass_qk_int8(t, t, t, t, 16, 16, 16, 1, 1, 1, 64, 64, 128, 0, 1, 32, 16, 4, 100, None)
+    assert rc < 0 and b"d_og" in lib.sage_last_error()
+    rc = lib.sage_prepass_qkv_fp8(t, t, t, t, 16, 16, 16, t, 16, 0, 0, 0, 16, 1, 1, 1, 64, 64, 64, 64, 0, 1, 32, 16, 4,
+                                  448.0, 72, None)
+    assert rc < 0 and b"d_og" in lib.sage_last_error()
     with pytest.raises(ValueError):
         _lib.check(-1)
 
