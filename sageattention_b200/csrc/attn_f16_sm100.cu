@@ -897,8 +897,12 @@ static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
   p.sm_scale_log2 = a->sm_scale * 1.44269504088896340736f;
 
   auto kern = sage_attn_fwd_kernel<D, kFp8>;
-  static bool attr_set = false;  // per template instantiation
-  if (!attr_set) {
+  // per template instantiation AND per device: function attributes belong to the device's context
+  static bool attr_set_dev[64] = {false};
+  int cur_dev = 0;
+  cudaGetDevice(&cur_dev);
+  bool& attr_set = attr_set_dev[(cur_dev >= 0 && cur_dev < 64) ? cur_dev : 0];
+  if (!attr_set || cur_dev >= 64) {
     SAGE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kDynamic));
     attr_set = true;
   }

@@ -56,3 +56,22 @@ def test_ulysses_two_gpus_matches_single_gpu():
     for rank, same, cos in res:
         assert same, f"rank {rank}: Ulysses output differs from the single-GPU operator"
         assert cos >= 0.999
+
+
+def test_two_devices_from_one_process():
+    """One process driving two GPUs (not the recommended layout, but the reference's core.py:583 supports it with
+    torch.cuda.set_device): per-device state of the library (function attributes, scheduler counters, SM count)
+    must not leak from the first device to the second."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    import sageattention_b200 as sb
+    g = torch.Generator().manual_seed(1)
+    q, k, v = (torch.randn(1, 4, 700, 128, generator=g).to(torch.bfloat16) for _ in range(3))
+    outs = []
+    for dev in ("cuda:0", "cuda:1", "cuda:0"):
+        o8 = sb.sageattn(q.to(dev), k.to(dev), v.to(dev), is_causal=True)
+        o16 = sb.sageattn_qk_int8_pv_fp16_cuda(q.to(dev), k.to(dev), v.to(dev))
+        torch.cuda.synchronize(dev)
+        outs.append((o8.cpu(), o16.cpu()))
+    for o8, o16 in outs[1:]:
+        assert torch.equal(o8, outs[0][0]) and torch.equal(o16, outs[0][1])
