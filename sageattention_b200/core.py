@@ -318,8 +318,8 @@ def sageattn_varlen(
     v16 = v.to(torch.float16)
     if smooth_k:
         k = k - k.mean(dim=0, keepdim=True)  # over all sequences of the pack, in the input dtype (core.py:462-463)
-    bq = cu_seqlens_q.tolist()
-    bk = cu_seqlens_k.tolist()
+    # one device-to-host copy for both length vectors (the only host synchronisation of the call)
+    bq, bk = torch.stack((cu_seqlens_q.to(torch.int64), cu_seqlens_k.to(torch.int64))).tolist()
     assert bq[-1] == q.size(0) and bk[-1] == k.size(0), "cu_seqlens do not cover the packed tensors"
     o = torch.empty(q.shape, dtype=dtype, device=q.device)
     for i in range(len(bq) - 1):
