@@ -299,7 +299,8 @@ def sageattn_varlen(
     of this entry point: every sequence runs through the fixed-length sm_100a kernels on
     views of the packed tensors (per-block quantiser launch + attention launch per sequence, output written
     in place into the packed result), so it costs one host synchronisation for the sequence lengths and
-    3 launches per sequence; a single-launch work list over cu_seqlens is the next step."""
+    3 launches per sequence - or 3 launches in all when every sequence of the pack has the same lengths (the
+    pack is then viewed as a [B, n, H, D] batch); a single-launch work list over cu_seqlens is the next step."""
     dtype = q.dtype
     assert q.is_cuda, "Input tensors must be on cuda."
     assert dtype in [torch.float16, torch.bfloat16], \
@@ -322,18 +323,27 @@ def sageattn_varlen(
     bq, bk = torch.stack((cu_seqlens_q.to(torch.int64), cu_seqlens_k.to(torch.int64))).tolist()
     assert bq[-1] == q.size(0) and bk[-1] == k.size(0), "cu_seqlens do not cover the packed tensors"
     o = torch.empty(q.shape, dtype=dtype, device=q.device)
-    for i in range(len(bq) - 1):
-        q0, q1, k0, k1 = bq[i], bq[i + 1], bk[i], bk[i + 1]
+    nb = len(bq) - 1
+    lq, lk = bq[1] - bq[0], bk[1] - bk[0]
+    if kwargs.get("_batched", True) and nb > 1 and lq > 0 and lk > 0 and \
+            all(bq[i + 1] - bq[i] == lq and bk[i + 1] - bk[i] == lk for i in range(nb)):
+        # every sequence has the same lengths: the pack IS a [B, n, H, D] batch - one quantiser launch per
+        # tensor and one attention launch for all of it (same tiles, same bits as the per-sequence launches)
+        ranges = [(0, q.size(0), 0, k.size(0), nb)]
+    else:
+        ranges = [(bq[i], bq[i + 1], bk[i], bk[i + 1], 1) for i in range(nb)]
+    for q0, q1, k0, k1, nseq in ranges:
         if q1 == q0:
             continue
         if k1 == k0:
             o[q0:q1].zero_()
             continue
-        assert q1 - q0 <= max_seqlen_q and k1 - k0 <= max_seqlen_k, "sequence longer than max_seqlen"
-        qi, ki, vi = q[q0:q1].unsqueeze(0), k[k0:k1].unsqueeze(0), v16[k0:k1].unsqueeze(0)  # [1, n, H, D] "NHD" views
+        assert (q1 - q0) // nseq <= max_seqlen_q and (k1 - k0) // nseq <= max_seqlen_k, "sequence longer than max_seqlen"
+        shp = lambda t, a, b_: t[a:b_].view(nseq, (b_ - a) // nseq, t.size(1), t.size(2))  # [B, n, H, D] "NHD" views
+        qi, ki, vi = shp(q, q0, q1), shp(k, k0, k1), shp(v16, k0, k1)
         q_int8, q_scale, k_int8, k_scale = per_block_int8(qi, ki, None, BLKQ=128, BLKK=64, sm_scale=sm_scale,
                                                           tensor_layout="NHD")
         # Q already carries sm_scale * log2 e: the kernel's own factor must be 1
-        _launch(False, q_int8, k_int8, vi, o[q0:q1].unsqueeze(0), q_scale, k_scale, None, None, "NHD", is_causal,
+        _launch(False, q_int8, k_int8, vi, shp(o, q0, q1), q_scale, k_scale, None, None, "NHD", is_causal,
                 _lib.GRAN_PER_BLOCK, 32, 1.0 / 1.44269504088896340736, False)
     return o[..., :head_dim_og]

@@ -74,3 +74,16 @@ def test_varlen_gqa_cross_lengths_and_errors():
         sb.sageattn_varlen(q, k, v, cq, ck, 1, 1)            # CPU tensors
     with pytest.raises(AssertionError):
         sb.sageattn_varlen(q.to(DEV).float(), k.to(DEV).float(), v.to(DEV).float(), cq.to(DEV), ck.to(DEV), 1000, 1000)
+
+
+@pytest.mark.parametrize("causal", [False, True])
+def test_varlen_equal_lengths_batched_equals_per_sequence(causal):
+    """A pack whose sequences all have the same lengths runs as ONE [B, n, H, D] batch (3 launches instead of
+    3 per sequence); the result must be bit-identical to the per-sequence launches."""
+    lens = [333] * 5
+    q, k, v, cq, ck = _pack(lens, lens, 4, 2, 128, torch.bfloat16, seed=21)
+    args = (q.to(DEV), k.to(DEV), v.to(DEV), cq.to(DEV), ck.to(DEV), 333, 333)
+    o_batched = sb.sageattn_varlen(*args, is_causal=causal)
+    o_loop = sb.sageattn_varlen(*args, is_causal=causal, _batched=False)
+    torch.cuda.synchronize()
+    assert torch.equal(o_batched, o_loop)
