@@ -7,9 +7,9 @@
 // with a from-scratch tcgen05 design (not a port):
 //
 //   * PERSISTENT grid (one CTA per SM): a work item is TWO 128-row Q tiles (256 query rows) of one
-//     (batch, head), walked over the KV sequence in 128-row tiles; every CTA takes items with stride
-//     gridDim.x (causal: mirror pairs of equal cost), barrier phases run on across items, and the
-//     issuer launches the next item's first Q.K^T under the current item's last step and epilogue;
+//     (batch, head), walked over the KV sequence in 128-row tiles; items come from a dynamic scheduler
+//     (attn_common_sm100.cuh), barrier phases run on across items, and the issuer launches the next
+//     item's first Q.K^T under the current item's last step and epilogue;
 //   * warp 8 is the TMA producer (a Q ring of two items, a K ring and a V ring, 128B-swizzled smem);
 //   * warp 9 is the single-thread MMA issuer:  S_t = Q_t.K^T  as tcgen05.mma kind::i8 (s32 in TMEM),
 //     O_t += P_t.V as kind::f8f6f4 (e4m3) or kind::f16, P read from shared memory;
@@ -38,25 +38,9 @@
 #include <cstring>
 #include <atomic>
 
-#include "../../include/sage_b200.h"
-#include "ptx_sm100.cuh"
-#include "softmax_sm100.cuh"
-#include "status.h"
+#include "attn_common_sm100.cuh"
 
 namespace sage {
-
-// Development aid (-DSAGE_TRACE, tools/trace_attn.py): SM-clock stamps of CTA 0's first kv steps
-// (counted across its work items; slots 8/9 = last P.V seen / end of the item's epilogue).
-#ifdef SAGE_TRACE
-constexpr int kTraceSteps = 64, kTraceSlots = 12;
-__device__ long long g_trace[3][kTraceSteps][kTraceSlots];
-#define SAGE_STAMP(who, j, slot)                                                             \
-  do {                                                                                       \
-    if (trace_on && (j) < kTraceSteps) g_trace[who][j][slot] = clock64();                    \
-  } while (0)
-#else
-#define SAGE_STAMP(who, j, slot) do { } while (0)
-#endif
 
 // 1 = the exp phases of the two softmax warpgroups alternate (named barriers), 0 = free-running.
 // (Whole-step alternation, a fixed phase offset and pre-biased S were measured slower and live in
@@ -78,38 +62,6 @@ __device__ long long g_trace[3][kTraceSteps][kTraceSlots];
 template <int D>
 constexpr bool kPTmem = (D == 64);
 
-constexpr int kTileQ = 128;       // rows per Q tile (= TMEM lanes)
-constexpr int kTileKV = 128;      // kv rows per step
-constexpr int kQStages = 2;      // Q tiles of the current and of the next work item
-constexpr int kKStages = 2;
-constexpr int kVStages = 2;
-constexpr int kSoftmaxThreads = 256;  // 2 warpgroups
-constexpr int kThreads = 384;         // + a third warpgroup: TMA warp, MMA warp, two idle warps
-// setmaxnreg: the launch gives every warp 168 registers; the third warpgroup hands most of its
-// share to the softmax warpgroups, whose exp loop needs the headroom to keep many logits in flight.
-constexpr int kSoftmaxRegs = 232;
-constexpr int kIssueRegs = 40;
-struct AttnKernelParams {
-  const float* q_scale;
-  const float* k_scale;
-  const float* v_scale;  // may be null
-  const float* v_mean;   // may be null
-  void* o;
-  float* lse;  // may be null
-  int* debug_s;  // may be null: raw S of kv tile 0, [B,Hq,ceil256(Nq),128] s32
-  int B, Hq, Hkv, Nq, Nk, Npad_v;
-  long long o_stride_b, o_stride_h, o_stride_n;  // elements
-  int q_scale_per_bh, k_scale_per_bh;            // entries per (b,h)
-  int gran;                                      // 1 per_block(128/64) 2 per_warp 3 per_thread
-  int warp_q;                                    // 16 or 32 rows per q-scale group (gran 2/3)
-  int causal;
-  int n_qpairs;  // ceil(Nq / 256)
-  int n_work;    // work items: B * Hq * n_qpairs
-  unsigned int* sched_counter;  // zero at launch; see g_sched_counter
-  int out_bf16;
-  float sm_scale_log2;
-};
-
 template <int D, bool kFp8>
 struct SmemLayout {
   static constexpr int kQBytes = kTileQ * D;                            // int8
@@ -130,128 +82,6 @@ struct SmemLayout {
   static constexpr int kTotal = kVsOff + 3 * 128 * 4;
   static constexpr int kDynamic = kTotal + 1024;  // slack for 1024B alignment
 };
-
-// ---------------------------------------------------------------------------------------------
-// Persistent work list with a dynamic scheduler.  A work item is one pair of Q tiles (256 query rows)
-// of one (batch, head).  The TMA producer thread owns the list: a CTA's first item is blockIdx.x,
-// every further one comes from an atomic counter (fetched one item ahead, so its latency is hidden),
-// is decoded there (the integer divisions stay off the softmax warps) and published to the other
-// warps through a small shared-memory ring guarded by mbarriers.
-//   non-causal: w -> (bh = w / n_qpairs, q_pair = w % n_qpairs): neighbours in time share K/V in L2
-//   causal:     heads in groups of kHeadGroup; inside a group the heavy (late) q pairs come first, so
-//               the list is longest-processing-time-first where it matters (the tail of the launch)
-//               while only a few heads' K/V are live in L2 at a time.
-constexpr int kSchedSlots = 3;
-constexpr int kHeadGroup = 8;
-constexpr int kSchedCounters = 1024;
-// One counter per launch in flight (the host rotates through them); the CTA that draws the last
-// ticket of a launch puts the counter back to zero.
-__device__ unsigned int g_sched_counter[kSchedCounters];
-
-struct __align__(16) WorkItem {
-  int q_pair, h, b, hkv;  // q_pair < 0: end of the list
-};
-__device__ __forceinline__ WorkItem decode_work(const AttnKernelParams& p, unsigned int w) {
-  WorkItem o;
-  if (w >= (unsigned int)p.n_work) {
-    o.q_pair = -1; o.h = 0; o.b = 0; o.hkv = 0;
-    return o;
-  }
-  int bh, qp;
-  if (!p.causal) {
-    bh = (int)w / p.n_qpairs;
-    qp = (int)w - bh * p.n_qpairs;
-  } else {
-    const int per_group = kHeadGroup * p.n_qpairs;
-    const int g = (int)w / per_group;
-    const int r = (int)w - g * per_group;
-    const int gsz = min(kHeadGroup, p.B * p.Hq - g * kHeadGroup);
-    const int level = r / gsz;
-    qp = p.n_qpairs - 1 - level;
-    bh = g * kHeadGroup + (r - level * gsz);
-  }
-  o.q_pair = qp;
-  o.b = bh / p.Hq;
-  o.h = bh - o.b * p.Hq;
-  o.hkv = o.h / (p.Hq / p.Hkv);
-  return o;
-}
-// consumer side of the ring (the slot stays valid until this thread arrives on sched_empty)
-__device__ __forceinline__ WorkItem read_work(const WorkItem* ring, uint64_t* sched_full, uint32_t it) {
-  mbar_wait(&sched_full[it % kSchedSlots], (it / kSchedSlots) & 1u);
-  const int4 v = ld_shared_v4(smem_u32(&ring[it % kSchedSlots]));
-  WorkItem o;
-  o.q_pair = v.x; o.h = v.y; o.b = v.z; o.hkv = v.w;
-  return o;
-}
-// kv tiles per q tile (causal: stop at the diagonal tile; top-left aligned as the reference,
-// /root/reference/csrc/qattn/qk_int_sv_f16_cuda_sm80.cu:218-222)
-__device__ __forceinline__ void item_iters(const AttnKernelParams& p, int q_pair, int (&n_it)[2]) {
-#pragma unroll
-  for (int t = 0; t < 2; ++t) {
-    const int qs = (q_pair * 2 + t) * kTileQ;
-    int kv_end = p.Nk;
-    if (p.causal) kv_end = min(kv_end, qs + kTileQ);
-    n_it[t] = (qs < p.Nq) ? (kv_end + kTileKV - 1) / kTileKV : 0;
-  }
-}
-
-// Running barrier phases of one softmax warpgroup across work items.
-struct WgState {
-  uint32_t steps;    // kv steps this warpgroup has finished (phase of s_full / s_free / p_full / p_empty)
-  uint32_t items;    // work items it has finished (phase of o_full)
-  bool granted;      // warpgroup 1: the first exp turn of the coming item is already granted
-};
-
-// What the step loop of one work item needs; prepared ahead of time (under the previous item's last
-// P.V) so that the global-load latency of the scales is off the item-to-item critical path.
-struct ItemCtx {
-  bool valid;
-  int n_iter;      // kv steps of this warpgroup's tile (0: tile is beyond Nq)
-  int n_pingpong;  // steps both warpgroups execute
-  bool next_pingpong;
-  int q_row;
-  float qs;        // q scale of the row (raw: the load is still in flight when setup returns)
-  const float* ksp;
-};
-template <int D>
-__device__ __forceinline__ ItemCtx softmax_setup(const AttnKernelParams& p, int t, int row,
-                                                 const WorkItem* ring, uint64_t* sched_full, uint32_t it) {
-  ItemCtx c;
-  const WorkItem wi = read_work(ring, sched_full, it);
-  c.valid = wi.q_pair >= 0;
-  c.n_iter = c.n_pingpong = 0;
-  c.next_pingpong = false;
-  c.q_row = 0;
-  c.qs = 0.f;
-  c.ksp = nullptr;
-  if (!c.valid) return c;
-  int n_it[2];
-  item_iters(p, wi.q_pair, n_it);
-  c.n_iter = n_it[t];
-  c.n_pingpong = min(n_it[0], n_it[1]);
-  {  // will both warpgroups alternate in the next item?  (the producer publishes one item ahead)
-    const WorkItem nx = read_work(ring, sched_full, it + 1);
-    if (nx.q_pair >= 0) {
-      int n_nx[2];
-      item_iters(p, nx.q_pair, n_nx);
-      c.next_pingpong = min(n_nx[0], n_nx[1]) > 0;
-    }
-  }
-  c.q_row = (wi.q_pair * 2 + t) * kTileQ + row;
-  {
-    const int sh = (p.warp_q == 16) ? 4 : 5;
-    int idx;
-    if (p.gran == 3) idx = (c.q_row >> sh) * 8 + (c.q_row & 7);
-    else if (p.gran == 2) idx = c.q_row >> sh;
-    else idx = c.q_row >> 7;
-    idx = min(idx, p.q_scale_per_bh - 1);
-    c.qs = __ldg(p.q_scale + (size_t)(wi.b * p.Hq + wi.h) * p.q_scale_per_bh + idx);  // first use: step 0
-  }
-  c.ksp = p.k_scale + (size_t)(wi.b * p.Hkv + wi.hkv) * p.k_scale_per_bh;
-  prefetch_l1(c.ksp);
-  return c;
-}
 
 // The kv steps of one work item for Q tile `t` (128 threads, thread = query row).
 template <int D, bool kFp8>
@@ -433,132 +263,6 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
 
   m_out = m_run;
   d_out = d_run;
-}
-
-// O row (f32, registers) -> 16-bit row in the 128B-swizzled staging tile.  Packed f32x2 arithmetic:
-// y = o * (1/d) [* v_scale] [+ v_mean], two columns per instruction, one F2FP per pair.
-template <int D, bool kBf16, bool kScale, bool kMean>
-__device__ __forceinline__ void epilogue_convert(const uint32_t (&o)[D], float inv_d, uint32_t vs_addr,
-                                                 const float* vmp, uint32_t orow, uint32_t ox) {
-  const uint64_t inv2 = pack2(inv_d, inv_d);
-#pragma unroll
-  for (int c0 = 0; c0 < D; c0 += 8) {
-    uint32_t packed[4];
-#pragma unroll
-    for (int i = 0; i < 8; i += 4) {
-      uint64_t y0 = fmul2(pack2(__uint_as_float(o[c0 + i]), __uint_as_float(o[c0 + i + 1])), inv2);
-      uint64_t y1 = fmul2(pack2(__uint_as_float(o[c0 + i + 2]), __uint_as_float(o[c0 + i + 3])), inv2);
-      uint64_t s0 = 0, s1 = 0, m0 = 0, m1 = 0;
-      if constexpr (kScale) {
-        const int4 f = ld_shared_v4(vs_addr + (uint32_t)(c0 + i) * 4u);
-        s0 = pack2(__int_as_float(f.x), __int_as_float(f.y));
-        s1 = pack2(__int_as_float(f.z), __int_as_float(f.w));
-      }
-      if constexpr (kMean) {
-        const float4 f = __ldg(reinterpret_cast<const float4*>(vmp + c0 + i));
-        m0 = pack2(f.x, f.y);
-        m1 = pack2(f.z, f.w);
-      }
-      if constexpr (kScale && kMean) {
-        y0 = ffma2(y0, s0, m0);
-        y1 = ffma2(y1, s1, m1);
-      } else if constexpr (kScale) {
-        y0 = fmul2(y0, s0);
-        y1 = fmul2(y1, s1);
-      } else if constexpr (kMean) {
-        y0 = fadd2(y0, m0);
-        y1 = fadd2(y1, m1);
-      }
-      float a0, a1, a2, a3;
-      unpack2(y0, a0, a1);
-      unpack2(y1, a2, a3);
-      if constexpr (kBf16) {
-        __nv_bfloat162 v0 = __floats2bfloat162_rn(a0, a1), v1 = __floats2bfloat162_rn(a2, a3);
-        packed[i >> 1] = *reinterpret_cast<uint32_t*>(&v0);
-        packed[(i >> 1) + 1] = *reinterpret_cast<uint32_t*>(&v1);
-      } else {
-        __half2 v0 = __floats2half2_rn(a0, a1), v1 = __floats2half2_rn(a2, a3);
-        packed[i >> 1] = *reinterpret_cast<uint32_t*>(&v0);
-        packed[(i >> 1) + 1] = *reinterpret_cast<uint32_t*>(&v1);
-      }
-    }
-    // 8 columns = one 16-byte chunk of 64-column block (c0 / 64); chunk c sits at c ^ (row & 7)
-    const uint32_t chunk = (uint32_t)((c0 & 63) >> 3);
-    const uint32_t addr = orow + (uint32_t)(c0 >> 6) * (kTileQ * 128) + ((chunk ^ ox) << 4);
-    st_shared_v4(addr, packed[0], packed[1], packed[2], packed[3]);
-  }
-}
-
-// Epilogue of one work item: O_t / d [* v_scale] [+ v_mean] -> 16-bit -> shared memory -> bulk tensor
-// store; LSE.  The issuer is already running the next item's Q.K^T under it; its first P.V (which
-// overwrites O_t) waits for this warpgroup's next P tile, i.e. for the loads done here.
-template <int D, bool kFp8>
-__device__ __forceinline__ void softmax_epilogue(const AttnKernelParams& p, int t, int row,
-                                                 const WorkItem* ring, uint32_t it, uint32_t tmem_base,
-                                                 uint8_t* o_smem, float* vs_smem, const CUtensorMap* tmO,
-                                                 uint64_t* o_full, WgState& st, float m_run, float d_run) {
-  const uint32_t tO = tmem_base + ((uint32_t)((row >> 5) * 32) << 16) + (uint32_t)(256 + t * D);
-  // the item's coordinates come back from the ring slot (still owned by this thread) instead of
-  // living in registers through the step loop
-  const int4 wv = ld_shared_v4(smem_u32(&ring[it % kSchedSlots]));
-  const int h = wv.y, b = wv.z, hkv = wv.w;
-  const int q_tile_start = (wv.x * 2 + t) * kTileQ;
-  const int q_row = q_tile_start + row;
-#ifdef SAGE_TRACE
-  const bool trace_on = blockIdx.x == 0 && row == 0;
-#endif
-  const float* vsp = p.v_scale ? p.v_scale + (size_t)(b * p.Hkv + hkv) * D : nullptr;
-  const float* vmp = p.v_mean ? p.v_mean + (size_t)(b * p.Hkv + hkv) * D : nullptr;
-  // per-channel factors: v_scale sits in the ring slot (bulk-copied by the producer together with the
-  // entry); the rarer v_mean is only prefetched here and read chunk by chunk below
-  if (vmp && (row & 31) < D / 32) prefetch_l1(vmp + (row & 31) * 32);
-  SAGE_STAMP(t, st.steps - 1, 10);
-  mbar_wait(&o_full[t], st.items & 1u);
-  ++st.items;
-  tc_fence_after();
-  SAGE_STAMP(t, st.steps - 1, 8);
-  const float inv_d = rcp_approx(d_run);
-  // The tile goes out through shared memory and ONE bulk tensor store per 64-column block (a thread
-  // owns a row, so direct stores would be 16 bytes per thread at a row pitch: measured 5-7 k cycles
-  // per item).  The previous item's store must have finished reading the staging tile first.
-  if (row == 0) tma_store_wait_read();
-  named_bar_sync(3 + t, kTileQ);
-  SAGE_STAMP(t, st.steps - 1, 11);
-  const uint32_t orow = smem_u32(o_smem) + (uint32_t)row * 128u;
-  const uint32_t ox = (uint32_t)(row & 7);
-  // all of O_t in one go: the four loads overlap, one wait
-  uint32_t oall[D];
-#pragma unroll
-  for (int c0 = 0; c0 < D; c0 += 32)
-    tmem_ld32(tO + c0, *reinterpret_cast<uint32_t(*)[32]>(&oall[c0]));
-  tc_wait_ld();
-  // one specialised conversion loop per (output type, v_scale?, v_mean?) instead of per-element selects
-  const uint32_t vs_addr = smem_u32(vs_smem);
-  const int variant = (p.out_bf16 ? 4 : 0) | (vsp ? 2 : 0) | (vmp ? 1 : 0);
-  switch (variant) {
-    case 0: epilogue_convert<D, false, false, false>(oall, inv_d, vs_addr, vmp, orow, ox); break;
-    case 1: epilogue_convert<D, false, false, true>(oall, inv_d, vs_addr, vmp, orow, ox); break;
-    case 2: epilogue_convert<D, false, true, false>(oall, inv_d, vs_addr, vmp, orow, ox); break;
-    case 3: epilogue_convert<D, false, true, true>(oall, inv_d, vs_addr, vmp, orow, ox); break;
-    case 4: epilogue_convert<D, true, false, false>(oall, inv_d, vs_addr, vmp, orow, ox); break;
-    case 5: epilogue_convert<D, true, false, true>(oall, inv_d, vs_addr, vmp, orow, ox); break;
-    case 6: epilogue_convert<D, true, true, false>(oall, inv_d, vs_addr, vmp, orow, ox); break;
-    default: epilogue_convert<D, true, true, true>(oall, inv_d, vs_addr, vmp, orow, ox); break;
-  }
-  fence_proxy_async_smem();
-  named_bar_sync(3 + t, kTileQ);
-  if (row == 0) {
-#pragma unroll
-    for (int c = 0; c < D / 64; ++c)
-      tma_store_4d(tmO, o_smem + c * (kTileQ * 128), c * 64, q_tile_start, h, b);
-    tma_store_commit();
-  }
-  const bool store = q_row < p.Nq;
-  tc_fence_before();
-  SAGE_STAMP(t, st.steps - 1, 9);
-  if (p.lse && store)
-    p.lse[(size_t)(b * p.Hq + h) * p.Nq + q_row] =
-        lg2_approx(d_run) + m_run - (kFp8 ? kFp8Offset : 0.f);
 }
 
 // ------------------------------------------------------------------------------------------
@@ -867,71 +571,6 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
 // ==========================================================================================
 namespace sage {
 
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
-                                  const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
-                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
-                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-static EncodeTiledFn get_encode_fn() {
-  static EncodeTiledFn fn = nullptr;
-  if (fn) return fn;
-  void* p = nullptr;
-  cudaDriverEntryPointQueryResult qres;
-  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) != cudaSuccess ||
-      qres != cudaDriverEntryPointSuccess)
-    return nullptr;
-  fn = reinterpret_cast<EncodeTiledFn>(p);
-  return fn;
-}
-
-// 4-D map: dims (inner, n, h, b); strides in BYTES for dims 1..3.
-static int make_map4(CUtensorMap* m, CUtensorMapDataType dt, void* ptr, uint64_t d0, uint64_t d1,
-                     uint64_t d2, uint64_t d3, uint64_t s1, uint64_t s2, uint64_t s3, uint32_t b0,
-                     uint32_t b1, CUtensorMapSwizzle swz, const char* name) {
-  EncodeTiledFn enc = get_encode_fn();
-  SAGE_REQUIRE(enc != nullptr, "cuTensorMapEncodeTiled entry point not available");
-  SAGE_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0, "%s: base pointer must be 16-byte aligned", name);
-  SAGE_REQUIRE(s1 % 16 == 0 && s2 % 16 == 0 && s3 % 16 == 0,
-               "%s: strides must be multiples of 16 bytes (got %llu %llu %llu)", name,
-               (unsigned long long)s1, (unsigned long long)s2, (unsigned long long)s3);
-  cuuint64_t dims[4] = {d0, d1, d2, d3};
-  cuuint64_t strides[3] = {s1, s2, s3};
-  cuuint32_t box[4] = {b0, b1, 1, 1};
-  cuuint32_t estr[4] = {1, 1, 1, 1};
-  CUresult r = enc(m, dt, 4, ptr, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
-                   CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  SAGE_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled(%s) failed with CUresult %d", name, (int)r);
-  return 0;
-}
-
-// SMs of the current device (the persistent grid runs one CTA on each)
-static int sm_count() {
-  static int cached[64] = {0};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (dev < 0 || dev >= 64) dev = 0;
-  if (cached[dev] == 0) {
-    int n = 0;
-    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
-    cached[dev] = n;
-  }
-  return cached[dev];
-}
-
-// device address of the scheduler counters on the current device
-static unsigned int* sched_counters() {
-  static unsigned int* cached[64] = {nullptr};
-  int dev = 0;
-  cudaGetDevice(&dev);
-  if (dev < 0 || dev >= 64) dev = 0;
-  if (cached[dev] == nullptr) {
-    void* ptr = nullptr;
-    if (cudaGetSymbolAddress(&ptr, g_sched_counter) != cudaSuccess) return nullptr;
-    cached[dev] = static_cast<unsigned int*>(ptr);
-  }
-  return cached[dev];
-}
-
 template <int D, bool kFp8>
 static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
   using L = SmemLayout<D, kFp8>;
@@ -1015,20 +654,6 @@ static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
   const int grid = (int)(n_work < sm_count() ? n_work : sm_count());
   kern<<<grid, kThreads, L::kDynamic, stream>>>(tmQ, tmK, tmV, tmO, p);
   SAGE_CUDA(cudaGetLastError());
-  return 0;
-}
-
-static int check_attn_args(const sage_attn_args* a) {
-  SAGE_REQUIRE(a != nullptr, "null args");
-  SAGE_REQUIRE(a->D == 64 || a->D == 128, "head_dim must be 64 or 128 after padding (got %d)", a->D);
-  SAGE_REQUIRE(a->B > 0 && a->Hq > 0 && a->Hkv > 0 && a->Nq > 0 && a->Nk > 0, "empty problem");
-  SAGE_REQUIRE(a->Hq % a->Hkv == 0, "num_qo_heads (%d) must be divisible by num_kv_heads (%d)", a->Hq, a->Hkv);
-  SAGE_REQUIRE(a->gran >= 1 && a->gran <= 3, "unsupported qk_quant_gran %d", a->gran);
-  SAGE_REQUIRE(a->gran == 1 || a->warp_q == 16 || a->warp_q == 32, "warp_q must be 16 or 32");
-  SAGE_REQUIRE(a->q8.ptr && a->k8.ptr && a->v.ptr && a->o.ptr && a->q_scale && a->k_scale, "null tensor pointer");
-  SAGE_REQUIRE(a->o.stride_n % 8 == 0 && a->o.stride_h % 8 == 0 && a->o.stride_b % 8 == 0 &&
-               (reinterpret_cast<uintptr_t>(a->o.ptr) & 15) == 0, "output rows must be 16-byte aligned");
-  SAGE_REQUIRE(a->B <= 65535 && a->Hq <= 65535, "batch / heads exceed grid limits");
   return 0;
 }
 
