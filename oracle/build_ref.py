@@ -130,6 +130,39 @@ def _drain(procs):
         print(f"[build_ref] compiled {os.path.basename(s)}")
 
 
+# The reference's Triton quantisers / varlen kernels are Python: "building" them for the GPU box means staging
+# the files, unmodified, next to the compiled .so files (oracle/_ref/stage/, git-ignored like the rest of
+# oracle/_ref, travels with gpurun).  Triton JIT-compiles them on the box.  Checker only, never product.
+TRITON_FILES = ["quant_per_thread.py", "quant_per_block.py", "quant_per_block_varlen.py",
+                "attn_qk_int8_block_varlen.py", "attn_qk_int8_per_block_causal_varlen.py",
+                "attn_qk_int8_per_block.py", "attn_qk_int8_per_block_causal.py",
+                "attn_qk_int8_per_thread.py", "attn_qk_int8_per_thread_causal.py"]
+
+
+def stage_triton():
+    src_dir = os.path.join(REF, "sageattention", "triton")
+    if not os.path.isdir(src_dir):
+        print(f"[build_ref] {src_dir} not present (GPU box?) - using staged files if any")
+        return
+    dst_dir = os.path.join(OUT, "stage")
+    os.makedirs(dst_dir, exist_ok=True)
+    for f in TRITON_FILES:
+        shutil.copyfile(os.path.join(src_dir, f), os.path.join(dst_dir, f))
+    print(f"[build_ref] staged {len(TRITON_FILES)} Triton reference files -> {dst_dir}")
+
+
+def load_triton(stem):
+    """Import a staged reference Triton module (e.g. "quant_per_thread"); None if not staged."""
+    import importlib.util
+    path = os.path.join(OUT, "stage", stem + ".py")
+    if not os.path.exists(path):
+        return None
+    spec = importlib.util.spec_from_file_location("ref_triton_" + stem, path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod
+
+
 def load(which):
     """Import a prebuilt oracle module from oracle/_ref (returns None if absent)."""
     import importlib.util
@@ -145,6 +178,9 @@ def load(which):
 
 
 if __name__ == "__main__":
-    todo = sys.argv[1:] or ["fused", "sm80", "sm89"]
+    todo = sys.argv[1:] or ["fused", "sm80", "sm89", "triton"]
     for w in todo:
-        build(w)
+        if w == "triton":
+            stage_triton()
+        else:
+            build(w)

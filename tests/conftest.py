@@ -45,6 +45,19 @@ def ref_sm89():
     return m
 
 
+@pytest.fixture(scope="session")
+def ref_triton():
+    """Loader of the reference's staged Triton modules (oracle/_ref/stage, see oracle/build_ref.py)."""
+    from oracle import build_ref
+
+    def get(stem):
+        m = build_ref.load_triton(stem)
+        if m is None:
+            pytest.skip(f"oracle/_ref/stage/{stem}.py not staged (python oracle/build_ref.py triton)")
+        return m
+    return get
+
+
 def accuracy(a, b):
     """(cosine similarity, relative L1, rmse) of a against b."""
     import torch

@@ -26,13 +26,7 @@ DEV = "cuda:0"
 
 
 def load_triton_ref():
-    stage = os.path.join(ROOT, "oracle", "_ref", "stage", "quant_per_thread.py")
-    if not os.path.exists(stage):
-        return None
-    spec = importlib.util.spec_from_file_location("ref_qpt", stage)
-    m = importlib.util.module_from_spec(spec)
-    spec.loader.exec_module(m)
-    return m
+    return build_ref.load_triton("quant_per_thread")
 
 
 def make_inputs(b, hq, hk, nq, nk, d, dtype, seed):

@@ -1,0 +1,225 @@
+"""GPU parity at the sizes BASELINE.json names, against the reference's OWN code run on the same B200
+(oracle/_ref: its sm80 / sm89 CUDA kernels and `_fused` quantisers compiled from /root/reference, and its
+Triton per-thread quantiser staged under oracle/_ref/stage).  A GPU-vs-GPU comparison needs no CPU oracle,
+so these run at C2 (B4 H32 N4096 D128), the C3 corners (N = 32768, hd64 / hd128, causal / full) and the
+DiT lengths of C4 / C5 (N = 119 056 ragged, N = 75 600).
+
+Tolerances (floating point; same gates as tests/test_attn_gpu.py):
+  fp16 P.V vs the sm80 kernel on identical codes: cos >= 0.9999, rel-L1 <= 1e-2, |dLSE| <= 2e-3 (base 2);
+  fp8  P.V vs the sm89 kernel on identical codes: cos >= 0.9995, rel-L1 <= 3e-2 (two independent e4m3
+  roundings of P), |dLSE| <= 2e-3, AND on a sample of query rows our distance to the fp64 result computed
+  from the same codes must be within 1.10x of the reference kernel's own distance.
+Quantiser codes and scales: BIT-EXACT.
+"""
+import pytest
+import torch
+
+import sageattention_b200 as sb
+from sageattention_b200 import core
+from oracle import sage_oracle as O
+from conftest import accuracy
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def make_qkv(b, hq, hk, nq, nk, d, dtype, seed, kbias=2.0):
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    q = torch.randn(b, hq, nq, d, generator=g, device=DEV)
+    k = torch.randn(b, hk, nk, d, generator=g, device=DEV) + kbias * torch.randn(1, hk, 1, d, generator=g, device=DEV)
+    v = torch.randn(b, hk, nk, d, generator=g, device=DEV)
+    return q.to(dtype), k.to(dtype), v.to(dtype)
+
+
+def exact_rows_from_codes(q8, k8, v, qs, ks, gran, causal, sm_scale, rows, bh, v_scale=None):
+    """fp64 attention of the query rows `rows` of one (batch, head) from the SAME codes and scales."""
+    b, h = bh
+    nq, nk, d = q8.size(2), k8.size(2), q8.size(3)
+    rows = torch.as_tensor(rows, device=DEV)
+    qi = O._scale_index(nq, gran, True, 32).clamp_max(qs.size(-1) - 1).to(DEV)
+    ki = O._scale_index(nk, gran, False).clamp_max(ks.size(-1) - 1).to(DEV)
+    s = q8[b, h, rows].double() @ k8[b, h].double().t()
+    s = s * qs[b, h].double()[qi[rows]][:, None] * ks[b, h].double()[ki][None, :] * sm_scale
+    if causal:
+        s = s.masked_fill(torch.arange(nk, device=DEV)[None, :] > rows[:, None], float("-inf"))
+    p = torch.softmax(s, dim=-1)
+    if v.dtype == torch.float8_e4m3fn:
+        inv = torch.tensor(O.PERM16).argsort().to(DEV)
+        npad = v.size(-1)
+        vt = v[b, h].float().reshape(d, npad // 16, 16)[..., inv].reshape(d, npad)
+        vf = vt.t()[:nk].double() * v_scale[b, h].double()[None, :]
+    else:
+        vf = v[b, h].double()
+    return p @ vf
+
+
+SIZES = [
+    # name, b, h, n, d, causal, dtype
+    ("C2", 4, 32, 4096, 128, False, torch.float16),
+    ("C3_hd128_full_32k", 1, 4, 32768, 128, False, torch.float16),
+    ("C3_hd128_causal_32k", 1, 4, 32768, 128, True, torch.float16),
+    ("C3_hd64_full_32k", 1, 4, 32768, 64, False, torch.float16),
+    ("C3_hd64_causal_32k", 1, 4, 32768, 64, True, torch.float16),
+    ("C4_hunyuan_len", 1, 2, 119056, 128, False, torch.bfloat16),
+    ("C5_wan_len", 1, 2, 75600, 128, False, torch.bfloat16),
+]
+
+
+@pytest.mark.parametrize("case", SIZES, ids=[c[0] for c in SIZES])
+def test_f16_kernel_vs_reference_sm80_at_baseline_sizes(ref_sm80, case):
+    _, b, h, n, d, causal, dtype = case
+    q, k, v = make_qkv(b, h, h, n, n, d, dtype, seed=n + d)
+    q8, qs, k8, ks, _ = sb.prepass_qk_int8(q, k, "per_thread", WARPQ=32)
+    v16 = v.to(torch.float16)
+    sm = d ** -0.5
+    o = torch.empty_like(q)
+    lse = core._launch(False, q8, k8, v16, o, qs, ks, None, None, "HND", causal, 3, 32, sm, True)
+    ro = torch.empty_like(q)
+    rlse = ref_sm80.qk_int8_sv_f16_accum_f32_attn(q8, k8, v16, ro, qs, ks, 1, int(causal), 3, sm, 1)
+    torch.cuda.synchronize()
+    assert torch.isfinite(o.float()).all()
+    # the reference leaves V rows beyond kv_len of the last tile uninitialised (attn_utils.cuh:130); compare where
+    # it is finite (all of it unless n is ragged)
+    ok = torch.isfinite(ro.float()).all(dim=-1)
+    if ok.float().mean().item() < 0.99:
+        pytest.skip("reference kernel produced non-finite values from uninitialised shared memory (ragged last tile)")
+    cos, l1, _ = accuracy(o[ok], ro[ok])
+    assert cos >= 0.9999 and l1 <= 1e-2, (cos, l1)
+    assert (lse - rlse)[ok].abs().max().item() <= 2e-3
+
+
+@pytest.mark.parametrize("case", SIZES, ids=[c[0] for c in SIZES])
+def test_f8_kernel_vs_reference_sm89_at_baseline_sizes(ref_sm89, case):
+    _, b, h, n, d, causal, dtype = case
+    q, k, v = make_qkv(b, h, h, n, n, d, dtype, seed=2 * n + d)
+    n_stat = (n + 127) // 128 * 128
+    q8, qs, k8, ks, _, v8, vs = sb.prepass_qkv_fp8(q, k, v, "per_thread", WARPQ=32, scale_max=448.0, _n_stat=n_stat)
+    sm = d ** -0.5
+    o = torch.empty_like(q)
+    lse = core._launch(True, q8, k8, v8, o, qs, ks, vs, None, "HND", causal, 3, 32, sm, True)
+    ro = torch.empty_like(q)
+    rlse = ref_sm89.qk_int8_sv_f8_accum_f32_fuse_v_scale_attn(q8, k8, v8, ro, qs, ks, vs, 1, int(causal), 3, sm, 1)
+    torch.cuda.synchronize()
+    assert torch.isfinite(o.float()).all() and torch.isfinite(ro.float()).all()
+    cos, l1, _ = accuracy(o, ro)
+    assert cos >= 0.9995 and l1 <= 3e-2, (cos, l1)
+    assert (lse - rlse).abs().max().item() <= 2e-3
+    # fp64 truth from the same codes on 384 query rows of the last (batch, head)
+    rows = torch.linspace(0, n - 1, 384).long().tolist()
+    bh = (b - 1, h - 1)
+    exact = exact_rows_from_codes(q8, k8, v8, qs, ks, 3, causal, sm, rows, bh, v_scale=vs)
+    _, l1_mine, _ = accuracy(o[bh[0], bh[1], rows], exact)
+    _, l1_ref, _ = accuracy(ro[bh[0], bh[1], rows], exact)
+    assert l1_mine <= 1.10 * l1_ref + 1e-4, (l1_mine, l1_ref)
+
+
+# ---------------------------------------------------------------------------------------------------
+# per_thread_int8 (the default qk_quant_gran) against the reference's Triton kernels, live and bit-exact
+# (reference: sageattention/triton/quant_per_thread.py:22-208)
+def _make(b, h, n, d, dtype, layout, seed, bias=2.0):
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    x = torch.randn(b, h, n, d, generator=g, device=DEV) + bias * torch.randn(1, h, 1, d, generator=g, device=DEV)
+    x = x.to(dtype)
+    return x.transpose(1, 2).contiguous() if layout == "NHD" else x
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("layout", ["HND", "NHD"])
+@pytest.mark.parametrize("n,d", [(256, 128), (1000, 128), (333, 64), (64, 64), (17, 128), (4096, 128), (75600, 128)])
+@pytest.mark.parametrize("warpq", [32, 16])
+def test_per_thread_bit_exact_vs_reference_triton(ref_triton, dtype, layout, n, d, warpq):
+    tri = ref_triton("quant_per_thread")
+    b, h = (1, 2) if n > 10000 else (2, 3)
+    q = _make(b, h, n, d, dtype, layout, 41)
+    k = _make(b, h, n + (37 if n < 10000 else 0), d, dtype, layout, 42)
+    sdim = 2 if layout == "HND" else 1
+    km = k.mean(dim=sdim)
+    for use_km in (km, None):
+        mine = sb.per_thread_int8(q, k, use_km, WARPQ=warpq, tensor_layout=layout)
+        ref = tri.per_thread_int8(q, k, None if use_km is None else use_km.unsqueeze(sdim), WARPQ=warpq,
+                                  tensor_layout=layout)
+        torch.cuda.synchronize()
+        assert torch.equal(mine[0], ref[0]), "q codes differ"
+        assert torch.equal(mine[2], ref[2]), "k codes differ"
+        # scale groups beyond the last row are never written by either implementation (torch.empty)
+        nq_groups = (n + warpq - 1) // warpq * 8
+        nk_groups = (k.size(sdim) + 63) // 64 * 4
+        assert torch.equal(mine[1][..., :nq_groups], ref[1][..., :nq_groups]), "q scales differ"
+        assert torch.equal(mine[3][..., :nk_groups], ref[3][..., :nk_groups]), "k scales differ"
+
+
+# ---------------------------------------------------------------------------------------------------
+# End to end: OUR operator vs THE REFERENCE'S OWN PIPELINE on the same q, k, v, both judged against fp32 SDPA.
+# Reference pipeline = upstream semantics of sageattn_qk_int8_pv_fp8_cuda / _fp16_cuda (core.py:590-651, 794-891):
+#   km = k.mean(seq) -> per_thread_int8 (the reference's Triton kernels) -> V: transpose_pad_permute +
+#   scale_fuse_quant (`_fused`)  -> the reference's sm89 / sm80 attention kernel.
+def reference_pipeline(tri, rf, r89, r80, q, k, v, causal, pv, pv_accum):
+    b, h, n, d = q.shape
+    nk = k.size(2)
+    sm = d ** -0.5
+    km = k.mean(dim=2, keepdim=True)
+    q8, qs, k8, ks = tri.per_thread_int8(q, k, km, BLKQ=128, WARPQ=32, BLKK=64, WARPK=64)
+    o = torch.empty_like(q)
+    if pv == "f16":
+        r80.qk_int8_sv_f16_accum_f32_attn(q8, k8, v.to(torch.float16), o, qs, ks, 1, int(causal), 3, sm, 0)
+        return o
+    n128 = (nk + 127) // 128 * 128
+    vpad = torch.cat([v, torch.zeros(b, k.size(1), n128 - nk, d, dtype=v.dtype, device=DEV)], dim=2) if n128 > nk else v
+    vt = torch.zeros((b, k.size(1), d, n128), dtype=v.dtype, device=DEV)
+    rf.transpose_pad_permute_cuda(vpad, vt, 1)
+    v8 = torch.zeros((b, k.size(1), d, n128), dtype=torch.float8_e4m3fn, device=DEV)
+    vs = torch.zeros((b, k.size(1), d), dtype=torch.float32, device=DEV)
+    smax = 2.25 if pv_accum == "fp32+fp16" else 448.0
+    rf.scale_fuse_quant_cuda(vt, v8, vs, n128, smax, 1)
+    fn = {"fp32": r89.qk_int8_sv_f8_accum_f32_fuse_v_scale_attn,
+          "fp32+fp32": r89.qk_int8_sv_f8_accum_f32_fuse_v_scale_attn_inst_buf,
+          "fp32+fp16": r89.qk_int8_sv_f8_accum_f16_fuse_v_scale_attn_inst_buf}[pv_accum]
+    fn(q8, k8, v8, o, qs, ks, vs, 1, int(causal), 3, sm, 0)
+    return o
+
+
+def dit_like_qkv(b, h, n, d, dtype, seed):
+    """SURVEY 8d's DiT-like input: K carries a per-channel bias and a few outlier channels (x20)."""
+    g = torch.Generator(device=DEV).manual_seed(seed)
+    q = torch.randn(b, h, n, d, generator=g, device=DEV)
+    k = torch.randn(b, h, n, d, generator=g, device=DEV) + 3.0 * torch.randn(1, h, 1, d, generator=g, device=DEV)
+    v = torch.randn(b, h, n, d, generator=g, device=DEV)
+    for c in (3, 17, 40, 59):
+        k[..., c] *= 20.0
+        q[..., c] *= 0.25   # keeps the logits in a sane range, as trained models do
+    return q.to(dtype), k.to(dtype), v.to(dtype)
+
+
+E2E = [
+    ("sageattn", {}, "f8", "fp32+fp32"),
+    ("sageattn_qk_int8_pv_fp8_cuda", {"pv_accum_dtype": "fp32"}, "f8", "fp32"),
+    ("sageattn_qk_int8_pv_fp8_cuda", {"pv_accum_dtype": "fp32+fp16"}, "f8", "fp32+fp16"),
+    ("sageattn_qk_int8_pv_fp16_cuda", {}, "f16", "fp32"),
+]
+RESULTS = []
+
+
+@pytest.mark.parametrize("fn,kw,pv,accum", E2E, ids=[f"{e[0]}-{e[3]}" for e in E2E])
+@pytest.mark.parametrize("data", ["randn", "dit_like"])
+@pytest.mark.parametrize("shape", [(2, 8, 2048, 128, False), (1, 8, 4096, 128, True), (2, 8, 2048, 64, False)],
+                         ids=["n2048_hd128", "n4096_hd128_causal", "n2048_hd64"])
+def test_operator_vs_reference_pipeline_vs_sdpa(ref_triton, ref_fused, ref_sm89, ref_sm80, fn, kw, pv, accum, data, shape):
+    """rel-L1 against fp32 SDPA of (a) our operator and (b) the reference's own quantisers + kernel on the same
+    q, k, v: ours must be within 1.05x of the reference pipeline's (plus 2e-4 absolute slack), and cos >= 0.999.
+    The measured pairs are printed (pytest -s) and summarised in BASELINE.md next to the north-star's 1e-2 gate."""
+    b, h, n, d, causal = shape
+    dtype = torch.bfloat16
+    if data == "randn":
+        q, k, v = make_qkv(b, h, h, n, n, d, dtype, seed=7 * n + d, kbias=2.0)
+    else:
+        q, k, v = dit_like_qkv(b, h, n, d, dtype, seed=9 * n + d)
+    truth = torch.nn.functional.scaled_dot_product_attention(q.float(), k.float(), v.float(), is_causal=causal)
+    ours = getattr(sb, fn)(q, k, v, is_causal=causal, **kw)
+    ref = reference_pipeline(ref_triton("quant_per_thread"), ref_fused, ref_sm89, ref_sm80, q, k, v, causal, pv, accum)
+    torch.cuda.synchronize()
+    cos_o, l1_o, _ = accuracy(ours, truth)
+    cos_r, l1_r, _ = accuracy(ref, truth)
+    print(f"[e2e] {fn} {accum} {data} {shape}: ours cos={cos_o:.6f} rel_l1={l1_o:.5f} | "
+          f"reference pipeline cos={cos_r:.6f} rel_l1={l1_r:.5f}")
+    assert cos_o >= 0.999, (cos_o, l1_o)
+    assert l1_o <= 1.05 * l1_r + 2e-4, (l1_o, l1_r)
