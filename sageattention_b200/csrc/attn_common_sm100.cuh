@@ -10,6 +10,9 @@
 #include <cuda_runtime.h>
 #include <atomic>
 #include <cstdint>
+#include <map>
+#include <mutex>
+#include <thread>
 #include <cstdio>
 #include <cstring>
 
@@ -61,7 +64,7 @@ struct AttnKernelParams {
   int causal;
   int n_qpairs;  // ceil(Nq / 256)
   int n_work;    // work items: B * Hq * n_qpairs
-  unsigned int* sched_counter;  // zero at launch; see g_sched_counter
+  unsigned int* sched_counter;  // zeroed on the launch stream just before the kernel; see g_sched_counter
   int out_bf16;
   float sm_scale_log2;
 };
@@ -79,10 +82,19 @@ struct AttnKernelParams {
 //               while only a few heads' K/V are live in L2 at a time.
 constexpr int kSchedSlots = 3;
 constexpr int kHeadGroup = 8;
-constexpr int kSchedCounters = 1024;
-// One counter per launch in flight (the host rotates through them); the CTA that draws the last
-// ticket of a launch puts the counter back to zero.
-static __device__ unsigned int g_sched_counter[kSchedCounters];  // one pool per translation unit
+// Ticket counters (one pool per translation unit and device, zero-initialised device memory).  Every launch
+// zeroes ITS counter with a cudaMemsetAsync on the launch stream just before the kernel (a memset node when
+// the launch is being captured), so a launch never depends on what an earlier one left behind.  Which counter:
+//   * eager launches: one slot per (stream, host thread for cudaStreamPerThread) - launches on one stream
+//     are serialised by the stream, launches on different streams never share a slot;
+//   * launches under stream capture: a fresh slot per captured launch that is never handed out again, so a
+//     replayed graph cannot collide with eager launches or with another graph (CUDA serialises replays of
+//     one executable graph).  The capture slots are finite (kSchedCaptureSlots per process and translation
+//     unit); running out is reported as an error, not wrapped around.
+constexpr int kSchedStreamSlots = 4096;
+constexpr int kSchedCaptureSlots = 61440;
+constexpr int kSchedCounters = kSchedStreamSlots + kSchedCaptureSlots;
+static __device__ unsigned int g_sched_counter[kSchedCounters];
 
 struct __align__(16) WorkItem {
   int q_pair, h, b, hkv;  // q_pair < 0: end of the list
@@ -359,30 +371,84 @@ static int make_map4(CUtensorMap* m, CUtensorMapDataType dt, void* ptr, uint64_t
 
 // SMs of the current device (the persistent grid runs one CTA on each)
 static int sm_count() {
-  static int cached[64] = {0};
+  static std::atomic<int> cached[64];
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64) dev = 0;
-  if (cached[dev] == 0) {
-    int n = 0;
+  int n = cached[dev].load(std::memory_order_relaxed);
+  if (n == 0) {
     if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
-    cached[dev] = n;
+    cached[dev].store(n, std::memory_order_relaxed);
   }
-  return cached[dev];
+  return n;
 }
 
-// device address of the scheduler counters on the current device
-static unsigned int* sched_counters() {
-  static unsigned int* cached[64] = {nullptr};
+// cudaFuncSetAttribute(max dynamic shared memory) once per (kernel instantiation = call site, device); racing
+// threads may both set it, which is harmless.
+struct SmemAttrOnce {
+  std::atomic<bool> done[64];
+  template <typename K>
+  cudaError_t ensure(K kern, int bytes) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const bool tracked = dev >= 0 && dev < 64;
+    if (tracked && done[dev].load(std::memory_order_acquire)) return cudaSuccess;
+    cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+    if (e == cudaSuccess && tracked) done[dev].store(true, std::memory_order_release);
+    return e;
+  }
+};
+
+// The scheduler counter of one launch on `stream` (see g_sched_counter); nullptr + message on failure.
+static unsigned int* acquire_sched_counter(cudaStream_t stream) {
+  struct Key {
+    int dev; cudaStream_t stream; std::thread::id tid;
+    bool operator<(const Key& o) const {
+      if (dev != o.dev) return dev < o.dev;
+      if (stream != o.stream) return stream < o.stream;
+      return tid < o.tid;
+    }
+  };
+  static std::mutex mu;
+  static std::map<Key, int> by_stream;
+  static int next_stream_slot = 0;
+  static int next_capture_slot[64] = {0};
+  static unsigned int* base[64] = {nullptr};
   int dev = 0;
   cudaGetDevice(&dev);
   if (dev < 0 || dev >= 64) dev = 0;
-  if (cached[dev] == nullptr) {
-    void* ptr = nullptr;
-    if (cudaGetSymbolAddress(&ptr, g_sched_counter) != cudaSuccess) return nullptr;
-    cached[dev] = static_cast<unsigned int*>(ptr);
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(stream, &cap) != cudaSuccess) {
+    cudaGetLastError();
+    cap = cudaStreamCaptureStatusNone;
   }
-  return cached[dev];
+  std::lock_guard<std::mutex> lock(mu);
+  if (base[dev] == nullptr) {
+    void* ptr = nullptr;
+    if (cudaGetSymbolAddress(&ptr, g_sched_counter) != cudaSuccess) {
+      fail_arg("cudaGetSymbolAddress(g_sched_counter) failed");
+      return nullptr;
+    }
+    base[dev] = static_cast<unsigned int*>(ptr);
+  }
+  int slot;
+  if (cap == cudaStreamCaptureStatusActive) {
+    if (next_capture_slot[dev] >= kSchedCaptureSlots) {
+      fail_arg("more than %d attention launches captured into CUDA graphs on device %d", kSchedCaptureSlots, dev);
+      return nullptr;
+    }
+    slot = kSchedStreamSlots + next_capture_slot[dev]++;
+  } else {
+    Key key{dev, stream, stream == cudaStreamPerThread ? std::this_thread::get_id() : std::thread::id()};
+    auto it = by_stream.find(key);
+    if (it == by_stream.end()) {
+      // more than kSchedStreamSlots distinct live streams would share slots; handles of destroyed streams are
+      // recycled by the driver, so in practice the map stays small
+      it = by_stream.emplace(key, next_stream_slot++ % kSchedStreamSlots).first;
+    }
+    slot = it->second;
+  }
+  return base[dev] + slot;
 }
 
 

@@ -24,6 +24,7 @@
 #include <cstdio>
 #include <cstring>
 #include <atomic>
+#include <type_traits>
 
 #include "attn_common_sm100.cuh"
 
@@ -35,7 +36,15 @@ using namespace sage;
 
 // The two softmax warpgroups run freely here (alternating their exp phases was measured slower with P
 // in TMEM).
+#ifndef SAGE_TURN
 #define SAGE_TURN 0
+#endif
+#ifndef SAGE_MAXTREE
+#define SAGE_MAXTREE 0
+#endif
+#ifndef SAGE_FUSE
+#define SAGE_FUSE 0
+#endif
 
 template <int D, bool kFp8>
 struct SmemLayout {
@@ -132,14 +141,39 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
     float alpha, bias[8], dsum;
     uint32_t w[kFp8 ? 32 : 64];
     if (masked_tile) softmax_max<kFp8, true, false>(s, sc, lim, m_run, alpha, bias);
+    else if (SAGE_MAXTREE) softmax_max_tree<kFp8>(s, sc, m_run, alpha, bias);
     else softmax_max<kFp8, false, false>(s, sc, 127, m_run, alpha, bias);
     SAGE_STAMP(t, st.steps, 5);
     // The exp phases of the two warpgroups alternate (they are the only MUFU-bound stretch): each
     // warpgroup's load / max / pack / store phases then run under the other one's exponentials.
     if (SAGE_TURN == 1 && j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
     SAGE_STAMP(t, st.steps, 6);
+#if SAGE_FUSE
+    // conversions issued group by group (16 columns) under the MUFU pipe; SAGE_FUSE == 2 also stores every group
+    // over the consumed S columns as soon as it is packed
+    auto window = [&](auto masked_c) {
+      constexpr bool kM = decltype(masked_c)::value;
+      uint64_t dsum2 = 0;
+#pragma unroll
+      for (int g = 0; g < 8; ++g) {
+        constexpr int kW = kFp8 ? 4 : 8;
+        uint32_t(&wg)[kW] = *reinterpret_cast<uint32_t(*)[kW]>(&w[SAGE_FUSE == 2 ? 0 : g * kW]);
+        softmax_exp_pack16<kFp8, kM>(g, s, sc, bias, kM ? lim : 127, dsum2, wg);
+        if (SAGE_FUSE == 2) {
+          if constexpr (kFp8) tmem_st4(tS + g * 4, *reinterpret_cast<uint32_t(*)[4]>(&wg[0]));
+          else tmem_st8(tS + g * 8, *reinterpret_cast<uint32_t(*)[8]>(&wg[0]));
+        }
+      }
+      float d0, d1;
+      unpack2(dsum2, d0, d1);
+      dsum = d0 + d1;
+    };
+    if (masked_tile) window(std::true_type{});
+    else window(std::false_type{});
+#else
     if (masked_tile) dsum = softmax_exp<true, 0, 128, 3, false>(s, sc, bias, lim);
     else dsum = softmax_exp<false, 0, 128, 3, false>(s, sc, bias, 127);
+#endif
     if (SAGE_TURN == 1 && j < n_pingpong) {
       if (t == 0) {
         named_bar_arrive(2, 2 * kTileQ);
@@ -152,7 +186,9 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
     }
     SAGE_STAMP(t, st.steps, 7);
     d_run = fmaf(d_run, alpha, dsum);
+#if !SAGE_FUSE
     softmax_pack<kFp8>(s, w);
+#endif
     SAGE_STAMP(t, st.steps, 3);
     // rescale O when some row of this warp moved its max (PV(j-1) is complete: S(j) was issued after
     // it and tcgen05.commit tracks all earlier MMAs)
@@ -170,7 +206,9 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
       }
     }
     // P row -> TMEM, over the S columns just consumed
-    if constexpr (kFp8) {
+    if (SAGE_FUSE == 2) {
+      // (stored group by group inside the window)
+    } else if constexpr (kFp8) {
       tmem_st32(tS, w);
     } else {
       uint32_t(&w0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&w[0]);
@@ -329,8 +367,6 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
           ++kc;
           ++vc;
           if (j == 0) {
-            // the launch's last ticket puts the counter back for the next launch
-            if (ticket == (unsigned int)p.n_work - 1u) *p.sched_counter = 0u;
             nxt = decode_work(p, gridDim.x + ticket);
             publish(ip + 1, nxt);
           }
@@ -537,24 +573,15 @@ static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
 
   auto kern = sage_attn_fwd_kernel<D, kFp8>;
   // per template instantiation AND per device: function attributes belong to the device's context
-  static bool attr_set_dev[64] = {false};
-  int cur_dev = 0;
-  cudaGetDevice(&cur_dev);
-  bool& attr_set = attr_set_dev[(cur_dev >= 0 && cur_dev < 64) ? cur_dev : 0];
-  if (!attr_set || cur_dev >= 64) {
-    SAGE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kDynamic));
-    attr_set = true;
-  }
+  static SmemAttrOnce smem_attr;
+  SAGE_CUDA(smem_attr.ensure(kern, L::kDynamic));
   p.n_qpairs = (a->Nq + 2 * kTileQ - 1) / (2 * kTileQ);
   const long long n_work = (long long)a->B * a->Hq * p.n_qpairs;
   SAGE_REQUIRE(n_work < (1ll << 31), "too many work items");
   p.n_work = (int)n_work;
-  {
-    static std::atomic<unsigned int> next_counter{0};
-    unsigned int* base = sched_counters();
-    SAGE_REQUIRE(base != nullptr, "cudaGetSymbolAddress(g_sched_counter) failed");
-    p.sched_counter = base + next_counter.fetch_add(1) % kSchedCounters;
-  }
+  p.sched_counter = acquire_sched_counter(stream);
+  if (p.sched_counter == nullptr) return -1;
+  SAGE_CUDA(cudaMemsetAsync(p.sched_counter, 0, sizeof(unsigned int), stream));
   const int grid = (int)(n_work < sm_count() ? n_work : sm_count());
   kern<<<grid, kThreads, L::kDynamic, stream>>>(tmQ, tmK, tmV, tmO, p);
   SAGE_CUDA(cudaGetLastError());

@@ -37,6 +37,7 @@
 #include <cstdio>
 #include <cstring>
 #include <atomic>
+#include <type_traits>
 
 #include "attn_common_sm100.cuh"
 
@@ -56,6 +57,17 @@ namespace sage {
 // k scales of later steps prefetched to L1: measured -0.7 %, off.
 #ifndef SAGE_KPREF
 #define SAGE_KPREF 0
+#endif
+
+// 1: the unmasked row maximum as depth-3 trees of 3-input maxima (40 independent first-level operations)
+#ifndef SAGE_MAXTREE
+#define SAGE_MAXTREE 0
+#endif
+// 0: exp, pack and store are separate phases.  1: the e4m3 / f16 conversions are issued group by group (16
+// columns) inside the exp phase, under the MUFU pipe.  2: as 1, and every group is stored (shared memory or
+// TMEM) as soon as it is packed, so that only the fence and the barrier arrival are left after the window.
+#ifndef SAGE_FUSE
+#define SAGE_FUSE 0
 #endif
 
 // P_t in its own TMEM columns (head_dim 64: S 256 + O 128 + P 64/128 columns) or in shared memory
@@ -173,10 +185,60 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
     if (p.causal) lim = min(lim, q_row - kv0);
     const bool masked_tile = (j == n_iter - 1) && (p.causal || (p.Nk - kv0) < kTileKV);
     float alpha, bias[8], dsum;
-    uint32_t w[kFp8 ? 32 : 64];
     if (masked_tile) softmax_max<kFp8, true, false>(s, sc, lim, m_run, alpha, bias);
+    else if (SAGE_MAXTREE) softmax_max_tree<kFp8>(s, sc, m_run, alpha, bias);
     else softmax_max<kFp8, false, false>(s, sc, 127, m_run, alpha, bias);
     SAGE_STAMP(t, st.steps, 5);
+    // shared-memory address of this row's P (K-major, 128B swizzle: 16B chunk c of row r sits at chunk c ^ (r & 7))
+    const uint32_t prow = smem_u32(p_smem) + (uint32_t)row * 128u;
+    const uint32_t px = (uint32_t)(row & 7);
+    const uint32_t tP = tmem_base + lane_off + (uint32_t)(384 + t * (kFp8 ? 32 : 64));  // kPTmem only
+#if SAGE_FUSE
+    // PV(j-1) complete: P tile reusable (checked before the window when the groups are stored inside it)
+    if (SAGE_FUSE == 2 && j > 0) mbar_wait(&p_empty[t], ph ^ 1u);
+    if (SAGE_TURN == 1 && j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
+    SAGE_STAMP(t, st.steps, 6);
+    uint32_t w[kFp8 ? 32 : 64];  // (SAGE_FUSE == 2 reuses the first group's words)
+    auto window = [&](auto masked_c) {
+      constexpr bool kM = decltype(masked_c)::value;
+      uint64_t dsum2 = 0;
+#pragma unroll
+      for (int g = 0; g < 8; ++g) {
+        constexpr int kW = kFp8 ? 4 : 8;
+        uint32_t(&wg)[kW] = *reinterpret_cast<uint32_t(*)[kW]>(&w[SAGE_FUSE == 2 ? 0 : g * kW]);
+        softmax_exp_pack16<kFp8, kM>(g, s, sc, bias, kM ? lim : 127, dsum2, wg);
+        if (SAGE_FUSE == 2) {
+          if constexpr (kPTmem<D>) {
+            if constexpr (kFp8) tmem_st4(tP + g * 4, *reinterpret_cast<uint32_t(*)[4]>(&wg[0]));
+            else tmem_st8(tP + g * 8, *reinterpret_cast<uint32_t(*)[8]>(&wg[0]));
+          } else {
+            // (this file's shared-memory P is e4m3: 16 columns = one 16-byte chunk)
+            st_shared_v4(prow + (((uint32_t)g ^ px) << 4), wg[0], wg[1], wg[2], wg[3]);
+          }
+        }
+      }
+      float d0, d1;
+      unpack2(dsum2, d0, d1);
+      dsum = d0 + d1;
+    };
+    if (masked_tile) window(std::true_type{});
+    else window(std::false_type{});
+    if (SAGE_TURN == 1 && j < n_pingpong) {
+      if (t == 0) {
+        named_bar_arrive(2, 2 * kTileQ);
+      } else if (j < n_pingpong - 1) {
+        named_bar_arrive(1, 2 * kTileQ);
+      } else if (next_pingpong) {
+        named_bar_arrive(1, 2 * kTileQ);
+        st.granted = true;
+      }
+    }
+    SAGE_STAMP(t, st.steps, 7);
+    d_run = fmaf(d_run, alpha, dsum);
+    SAGE_STAMP(t, st.steps, 3);
+    if (SAGE_FUSE != 2 && j > 0) mbar_wait(&p_empty[t], ph ^ 1u);
+#else
+    uint32_t w[kFp8 ? 32 : 64];
     // The exp phases of the two warpgroups alternate (they are the only MUFU-bound stretch): each
     // warpgroup's load / max / pack / store phases then run under the other one's exponentials.
     if (SAGE_TURN == 1 && j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
@@ -200,27 +262,24 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
     // PV(j-1) complete: P tile reusable and O_t stable (at j == 0 the epilogue of the previous item
     // has already waited for that item's last PV)
     if (j > 0) mbar_wait(&p_empty[t], ph ^ 1u);
+#endif
     // P leaves the registers first (w[] is dead after this) ...
-    if constexpr (kPTmem<D>) {
-      // head_dim 64 leaves 128 TMEM columns free: P_t gets its own columns there (no shared-memory
-      // store, no proxy fence, and the P.V MMA reads A from TMEM instead of the shared-memory port)
-      const uint32_t tP = tmem_base + lane_off + (uint32_t)(384 + t * (kFp8 ? 32 : 64));
-      if constexpr (kFp8) {
-        tmem_st32(tP, w);
+    if (SAGE_FUSE != 2) {
+      if constexpr (kPTmem<D>) {
+        // head_dim 64 leaves 128 TMEM columns free: P_t gets its own columns there (no shared-memory
+        // store, no proxy fence, and the P.V MMA reads A from TMEM instead of the shared-memory port)
+        if constexpr (kFp8) {
+          tmem_st32(tP, *reinterpret_cast<uint32_t(*)[32]>(&w[0]));
+        } else {
+          tmem_st32(tP, *reinterpret_cast<uint32_t(*)[32]>(&w[0]));
+          tmem_st32(tP + 32, *reinterpret_cast<uint32_t(*)[32]>(&w[kFp8 ? 0 : 32]));
+        }
       } else {
-        uint32_t(&w0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&w[0]);
-        uint32_t(&w1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&w[32]);
-        tmem_st32(tP, w0);
-        tmem_st32(tP + 32, w1);
-      }
-    } else {
-      // P row -> smem, K-major 128B-swizzled (16B chunk c of row r sits at chunk c ^ (r & 7))
-      const uint32_t prow = smem_u32(p_smem) + (uint32_t)row * 128u;
-      const uint32_t x = (uint32_t)(row & 7);
 #pragma unroll
-      for (int c = 0; c < (kFp8 ? 8 : 16); ++c) {
-        const uint32_t addr = prow + (uint32_t)(c >> 3) * (kTileQ * 128) + (((uint32_t)(c & 7) ^ x) << 4);
-        st_shared_v4(addr, w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
+        for (int c = 0; c < (kFp8 ? 8 : 16); ++c) {
+          const uint32_t addr = prow + (uint32_t)(c >> 3) * (kTileQ * 128) + (((uint32_t)(c & 7) ^ px) << 4);
+          st_shared_v4(addr, w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
+        }
       }
     }
     // ... then O is rescaled when some row of this warp moved its max ...
@@ -409,8 +468,6 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
           ++kc;
           ++vc;
           if (j == 0) {
-            // the launch's last ticket puts the counter back for the next launch
-            if (ticket == (unsigned int)p.n_work - 1u) *p.sched_counter = 0u;
             nxt = decode_work(p, gridDim.x + ticket);
             publish(ip + 1, nxt);
           }
@@ -633,24 +690,15 @@ static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
 
   auto kern = sage_attn_fwd_kernel<D, kFp8>;
   // per template instantiation AND per device: function attributes belong to the device's context
-  static bool attr_set_dev[64] = {false};
-  int cur_dev = 0;
-  cudaGetDevice(&cur_dev);
-  bool& attr_set = attr_set_dev[(cur_dev >= 0 && cur_dev < 64) ? cur_dev : 0];
-  if (!attr_set || cur_dev >= 64) {
-    SAGE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::kDynamic));
-    attr_set = true;
-  }
+  static SmemAttrOnce smem_attr;
+  SAGE_CUDA(smem_attr.ensure(kern, L::kDynamic));
   p.n_qpairs = (a->Nq + 2 * kTileQ - 1) / (2 * kTileQ);
   const long long n_work = (long long)a->B * a->Hq * p.n_qpairs;
   SAGE_REQUIRE(n_work < (1ll << 31), "too many work items");
   p.n_work = (int)n_work;
-  {
-    static std::atomic<unsigned int> next_counter{0};
-    unsigned int* base = sched_counters();
-    SAGE_REQUIRE(base != nullptr, "cudaGetSymbolAddress(g_sched_counter) failed");
-    p.sched_counter = base + next_counter.fetch_add(1) % kSchedCounters;
-  }
+  p.sched_counter = acquire_sched_counter(stream);
+  if (p.sched_counter == nullptr) return -1;
+  SAGE_CUDA(cudaMemsetAsync(p.sched_counter, 0, sizeof(unsigned int), stream));
   const int grid = (int)(n_work < sm_count() ? n_work : sm_count());
   kern<<<grid, kThreads, L::kDynamic, stream>>>(tmQ, tmK, tmV, tmO, p);
   SAGE_CUDA(cudaGetLastError());

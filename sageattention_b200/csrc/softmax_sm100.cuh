@@ -80,6 +80,48 @@ __device__ __forceinline__ void softmax_max(uint32_t (&s)[128], const float (&sc
   for (int k = 0; k < 8; ++k) bias[k] = fmaf(-kMagicF, sc[k], (kFp8 ? kFp8Offset : 0.f) - m_new);
 }
 
+// Integer maximum of the 16 columns of k-scale class `k` as a depth-3 tree of 3-input maxima (VIMNMX3): the
+// eight classes give 40 independent first-level operations, so a warp that has its scheduler to itself is
+// bound by the ALU pipe instead of by an 8-deep dependent chain per class.
+template <int kCls>
+__device__ __forceinline__ int class_max_tree(const uint32_t (&s)[128]) {
+  // columns of class k: block (k >> 2), (c & 7) >> 1 == (k & 3)  ->  c = blk*64 + 8*i + 2*(k&3) + {0,1}
+  constexpr int base = (kCls >> 2) * 64 + 2 * (kCls & 3);
+  auto e = [&](int n) { return (int)s[base + 8 * (n >> 1) + (n & 1)]; };
+  const int m0 = max(max(e(0), e(1)), e(2));
+  const int m1 = max(max(e(3), e(4)), e(5));
+  const int m2 = max(max(e(6), e(7)), e(8));
+  const int m3 = max(max(e(9), e(10)), e(11));
+  const int m4 = max(max(e(12), e(13)), e(14));
+  const int r0 = max(max(m0, m1), m2);
+  const int r1 = max(max(m3, m4), e(15));
+  return max(r0, r1);
+}
+
+// softmax_max for an unmasked tile with the tree maxima (same results as softmax_max<kFp8, false>).
+template <bool kFp8>
+__device__ __forceinline__ void softmax_max_tree(const uint32_t (&s)[128], const float (&sc)[8],
+                                                 float& m_run, float& alpha, float (&bias)[8]) {
+  int mx[8];
+  mx[0] = class_max_tree<0>(s); mx[1] = class_max_tree<1>(s); mx[2] = class_max_tree<2>(s); mx[3] = class_max_tree<3>(s);
+  mx[4] = class_max_tree<4>(s); mx[5] = class_max_tree<5>(s); mx[6] = class_max_tree<6>(s); mx[7] = class_max_tree<7>(s);
+  float cand[8];
+#pragma unroll
+  for (int k = 0; k < 8; ++k) cand[k] = (float)mx[k] * sc[k];
+  const float mrow = fmaxf(fmaxf(fmaxf(cand[0], cand[1]), fmaxf(cand[2], cand[3])),
+                           fmaxf(fmaxf(cand[4], cand[5]), fmaxf(cand[6], cand[7])));
+  const bool grow = mrow > m_run + (kFp8 ? kFp8Tau : kF16Tau);
+  float m_new = m_run;
+  alpha = 1.0f;
+  if (__any_sync(0xffffffffu, grow)) {
+    m_new = fmaxf(m_run, mrow);
+    alpha = ex2_approx(m_run - m_new);
+  }
+  m_run = m_new;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) bias[k] = fmaf(-kMagicF, sc[k], (kFp8 ? kFp8Offset : 0.f) - m_new);
+}
+
 // 2^y for a pair of logits on the FMA pipe (defined below)
 template <int kDeg>
 __device__ __forceinline__ uint64_t exp2_poly2(uint64_t y2);
@@ -140,6 +182,43 @@ __device__ __forceinline__ float softmax_exp(uint32_t (&s)[128], const float (&s
   }
   if (SAGE_PACKED) unpack2(dsum2, dsum0, dsum1);
   return dsum0 + dsum1;
+}
+
+// Phases 2 + 3 fused for one group of 16 columns (kG = 0..7): p = 2^(s * sc + bias), row-sum partials, and
+// the group's packed words (4 e4m3 words / 8 f16 words; kG must be a constant after unrolling) - so the conversions (ALU pipe) are issued in the shadow
+// of the exponentials (MUFU pipe) instead of after them, and the caller can store the group at once.
+template <bool kFp8, bool kMasked>
+__device__ __forceinline__ void softmax_exp_pack16(const int kG, uint32_t (&s)[128], const float (&sc)[8],
+                                                   const float (&bias)[8], int lim, uint64_t& dsum2,
+                                                   uint32_t (&w)[kFp8 ? 4 : 8]) {
+#pragma unroll
+  for (int i = 0; i < 16; i += 2) {
+    const int c = kG * 16 + i;
+    const float x0 = __int_as_float((int)s[c] + kMagicI);
+    const float x1 = __int_as_float((int)s[c + 1] + kMagicI);
+    float y0, y1;
+    unpack2(ffma2(pack2(x0, x1), pack2(sc[kcls(c)], sc[kcls(c)]), pack2(bias[kcls(c)], bias[kcls(c)])), y0, y1);
+    float p0 = ex2_approx(y0), p1 = ex2_approx(y1);
+    if constexpr (kMasked) {
+      p0 = (c > lim) ? 0.f : p0;
+      p1 = (c + 1 > lim) ? 0.f : p1;
+    }
+    dsum2 = fadd2(dsum2, pack2(p0, p1));
+    s[c] = __float_as_uint(p0);
+    s[c + 1] = __float_as_uint(p1);
+  }
+  if constexpr (kFp8) {
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int t = kG * 16 + 2 * q;
+      w[q] = pack_e4m3x4(__uint_as_float(s[t]), __uint_as_float(s[t + 1]), __uint_as_float(s[t + 8]),
+                         __uint_as_float(s[t + 9]));
+    }
+  } else {
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      w[i] = pack_f16x2(__uint_as_float(s[kG * 16 + 2 * i]), __uint_as_float(s[kG * 16 + 2 * i + 1]));
+  }
 }
 
 // Phase 3: pack p to e4m3 (32 words) / f16 (64 words).
