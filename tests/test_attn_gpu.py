@@ -342,3 +342,49 @@ def test_long_sequence_size_independent_properties(pv, d):
     o2 = run_kernel(pv, q8, qs, k8, ks, v2, vs2, None, 3, False, sm, torch.bfloat16)
     torch.cuda.synchronize()
     assert torch.equal(o2.float(), o1.float() * 2.0)
+
+
+@pytest.mark.parametrize("pv", ["f8", "f16"])
+def test_graph_replay_overlapping_eager_launches_on_another_stream(pv):
+    """The persistent scheduler's ticket counter is per launch: a captured launch owns a slot of its own, eager
+    launches use their stream's slot, and every launch zeroes its counter on its own stream first
+    (attn_common_sm100.cuh, acquire_sched_counter).  So a graph replayed on stream A while eager calls loop on
+    stream B - more of them than the old 1024-entry rotation held - must both keep producing the right output.
+    With a shared counter, tickets interleave: items are skipped and rows of the output are never written."""
+    a_in = _random_codes(1, 8, 8, 1536, 1536, 128, pv, seed=21)    # 48 items on 148 SMs: leaves room to overlap
+    b_in = _random_codes(1, 8, 8, 1280, 1280, 128, pv, seed=22)
+    sm = 128 ** -0.5
+
+    def launch(inp, o):
+        q8, qs, k8, ks, v, vs = inp
+        core._launch(pv == "f8", q8, k8, v, o, qs, ks, vs, None, "HND", True, 3, 32, sm, False)
+
+    oa_ref = torch.empty(a_in[0].shape, dtype=torch.float16, device=DEV)
+    ob_ref = torch.empty(b_in[0].shape, dtype=torch.float16, device=DEV)
+    launch(a_in, oa_ref)
+    launch(b_in, ob_ref)
+    torch.cuda.synchronize()
+    oa = torch.empty_like(oa_ref)
+    ob = torch.empty_like(ob_ref)
+    sa, sb_ = torch.cuda.Stream(), torch.cuda.Stream()
+    with torch.cuda.stream(sa):
+        launch(a_in, oa)            # warm-up on the capture stream
+    sa.synchronize()
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g, stream=sa):
+        launch(a_in, oa)
+    torch.cuda.synchronize()
+    bad = 0
+    for rnd in range(6):
+        oa.fill_(float("nan"))
+        ob.fill_(float("nan"))
+        torch.cuda.synchronize()
+        with torch.cuda.stream(sa):
+            for _ in range(40):
+                g.replay()
+        with torch.cuda.stream(sb_):
+            for _ in range(200):     # 6 x 200 = 1200 eager launches in all: past the old pool size
+                launch(b_in, ob)
+        torch.cuda.synchronize()
+        bad += int(not torch.equal(oa, oa_ref)) + int(not torch.equal(ob, ob_ref))
+    assert bad == 0

