@@ -59,6 +59,20 @@ size_t sage_seq_mean_workspace_bytes(int B, int H, int N, int D);
 int sage_seq_mean(sage_tensor4 x, void* out, int B, int H, int N, int D, int dtype, void* workspace,
                   void* stream);
 
+/* sage_seq_mean without a workspace argument and without any allocation.
+ * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arithmetic and
+ * bit-identical result as sage_seq_mean; the reduction scratch is a static device array of
+ * SAGE_SEQ_MEAN_STATIC_MAX_BYTES inside the library, which every GPU that loads the library holds until exit.
+ * The call makes no cudaMalloc / cudaFree / allocating library call; the caller still passes x and out.
+ * Limit: B*H*ceil(N/256)*3*D*4 + B*H*4 + 256 bytes must fit the array, else -1 with a message naming both sizes
+ * (Wan2.1 K, B1 H40 N75600 D128, needs 18.2 MB; HunyuanVideo, B1 H24 N119056 D128, 17.2 MB).
+ * All calls on a device SHARE the array: calls that overlap on the GPU (different streams, concurrent graph
+ * replays) race; serialise them on one stream or use sage_seq_mean with a workspace each.  The first call on a
+ * device resolves the array's device address (cudaGetSymbolAddress): make it once at set-up, outside capture. */
+#define SAGE_SEQ_MEAN_STATIC_MAX_BYTES (32u << 20)
+int sage_seq_mean_static(sage_tensor4 x, void* out, int B, int H, int N, int D, int dtype, void* stream);
+
 /* INT8 quantisation of rows in groups of `block` tokens (block in {16,32,64,128}).
  *   x' = float(x) [- float(mean[b,h,d])] [* sm_scale]   (mean may be NULL; has_sm_scale 0/1)
  *   amax = max(1e-7, max|x'|); scale = amax/127; code = cvt.rni.sat.s8(x' * (127/amax))

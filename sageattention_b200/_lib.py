@@ -38,6 +38,7 @@ SIGNATURES = {
     "sage_version": (c_int, []),
     "sage_seq_mean_workspace_bytes": (ctypes.c_size_t, [c_int] * 4),
     "sage_seq_mean": (c_int, [Tensor4, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp]),
+    "sage_seq_mean_static": (c_int, [Tensor4, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp]),
     "sage_quant_int8": (c_int, [Tensor4, c_vp, Tensor4, c_vp, c_int, c_int, c_int, c_int, c_int, c_int,
                                 c_int, c_int, c_f32, c_vp]),
     "sage_quant_per_thread_int8": (c_int, [Tensor4, c_vp, Tensor4, c_vp, c_int, c_int, c_int, c_int, c_int,
@@ -60,7 +61,7 @@ _lib = None
 # kernels launched by one call of each entry point (cudaMemsetAsync is not counted); LAUNCHES is
 # bumped on every call so bench.py can report how many of OUR kernels ran in its timed region.
 KERNELS_PER_CALL = {
-    "sage_seq_mean": 1, "sage_quant_int8": 1, "sage_quant_per_thread_int8": 1, "sage_sub_mean": 1,
+    "sage_seq_mean": 1, "sage_seq_mean_static": 1, "sage_quant_int8": 1, "sage_quant_per_thread_int8": 1, "sage_sub_mean": 1,
     "sage_smooth_quant_k_int8": 1, "sage_prepass_qk_int8": 1, "sage_prepass_qkv_fp8": 1,
     # smooth_v: statistics + conversion; otherwise one cluster launch
     "sage_per_channel_fp8": (lambda a: 2 if a[14] else 1),
