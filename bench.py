@@ -1,6 +1,6 @@
 """bench.py - the measurement contract for the SageAttention hot path on B200.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload NAME] [--no-sweep]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload NAME] [--no-sweep] [--no-sp]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
 A "step" is one pass of the hot path (quantisation pre-pass + fused INT8-QK / online-softmax / PV
@@ -16,6 +16,11 @@ value   = whole-job TOPS of the full operator call with q/k/v already resident i
 e2e     = same metric through the public API with HOST (pinned) q/k/v: H2D of the inputs and D2H of
           the output are inside the timed region of every step
 roofline= the attention kernel alone (CUDA events around its launch inside the timed steps)
+sweep   = (N=1) the metric's whole range measured in the same run: hd {64,128} x {full, causal} x N 1K..32K x PV
+          {fp8, f16}, kernel-only and whole-operator (public API, no graph replay) TOPS, clocks per entry
+sp      = the Wan2.1 DiT layer (B1 H40 N75600 hd128 bf16): on one GPU at N=1, under Ulysses sequence parallelism
+          (NCCL all-to-all) at N>1 with the collective timed alone and the efficiency against one GPU
+roofline.measured_ceilings = dense INT8 / FP8 / bf16 GEMM throughput of this GPU measured in this run
 cpu_baseline / --impl reference = the CPU restatement of the reference algorithm (oracle/, "port":
           the reference has no CPU implementation of this path) on the host cores, on a
           bounded sample of the same workload.
@@ -45,6 +50,8 @@ WORKLOADS = {
 # per workload (profiles/r1b_ncu_attn_f16_c2_summary.txt, r1b_ncu_attn_f8_c3_summary.txt: the persistent
 # kernels); algorithmic bytes at C2 fp16 = 402.7e6
 NCU_TRAFFIC = {"c2_fp16": 377.14e6, "c3_fp8": 302.79e6}
+NCU_TRAFFIC_SOURCE = {"c2_fp16": "ncu capture profiles/r1b_ncu_attn_f16_c2_summary.txt (not measured in this run)",
+                      "c3_fp8": "ncu capture profiles/r1b_ncu_attn_f8_c3_summary.txt (not measured in this run)"}
 METRIC = "attention TOPS @hd64/hd128 seq 1K-32K (causal/non-causal), % of INT8/FP8 tensor peak"
 
 
@@ -96,23 +103,18 @@ class ClockSampler:
         while self.proc is not None and not self.lines and time.monotonic() - t0 < timeout:
             time.sleep(0.01)
 
-    def stop(self, t_begin=None, t_end=None):
+    def window(self, t_begin=None, t_end=None):
+        """Summary of the samples taken in [t_begin, t_end] (monotonic clock); the sampler keeps running."""
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except Exception:
-            self.proc.kill()
         sm, mx, pw, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        # only samples taken inside the timed region count; a region shorter than the 50 ms sampling
-        # period falls back to the samples within 100 ms of it
-        lines = self.lines
+        # only samples taken inside the window count; a window shorter than the 50 ms sampling period falls
+        # back to the samples within 100 ms of it
+        lines = list(self.lines)
         if t_begin is not None:
-            lines = [(ts, ln) for ts, ln in self.lines if t_begin <= ts <= t_end]
-            if not lines:
-                lines = [(ts, ln) for ts, ln in self.lines if t_begin - 0.1 <= ts <= t_end + 0.1]
+            inside = [(ts, ln) for ts, ln in lines if t_begin <= ts <= t_end]
+            lines = inside or [(ts, ln) for ts, ln in lines if t_begin - 0.1 <= ts <= t_end + 0.1]
         for ts, ln in lines:
             f = [x.strip() for x in ln.split(",")]
             if len(f) < 7:
@@ -126,6 +128,201 @@ class ClockSampler:
                     reasons.add(nm)
         return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "power_w_max": max(pw) if pw else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+    def stop(self, t_begin=None, t_end=None):
+        out = self.window(t_begin, t_end)
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except Exception:
+                self.proc.kill()
+        return out
+
+
+def workload_string(name):
+    """The SAME string in both arms (ours and --impl reference), so the driver's same_config check can hold."""
+    api, b, h, n, d, causal, dtype_name = WORKLOADS[name]
+    return f"{name}: {api} B={b} H={h} N={n} D={d} causal={causal} {dtype_name}"
+
+
+def measure_ceilings(dev):
+    """Dense INT8 and FP8 GEMM ceilings of THIS GPU, measured in this run (torch._int_mm and
+    torch._scaled_mm at 8192^3, best of 10, CUDA events), next to a bf16 matmul taken the same way.  These are
+    library GEMMs used as roofline denominators only; nothing on the product path calls them."""
+    import torch
+    n = 8192
+    out = {"shape": f"{n}^3", "how": "best of 10 after 3 warm-ups, CUDA events, 2*N^3 ops"}
+
+    def best(fn):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        ts = []
+        for _ in range(10):
+            a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b_.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b_))
+        return 2.0 * n ** 3 / (min(ts) * 1e-3) * 1e-12
+
+    try:
+        x = torch.randn(n, n, device=dev, dtype=torch.bfloat16)
+        y = torch.randn(n, n, device=dev, dtype=torch.bfloat16)
+        out["bf16_tflops"] = best(lambda: torch.matmul(x, y))
+    except Exception as e:  # pragma: no cover
+        out["bf16_tflops"], out["bf16_error"] = None, f"{type(e).__name__}: {e}"[:160]
+    try:
+        a8 = torch.randint(-100, 100, (n, n), device=dev, dtype=torch.int8)
+        b8 = torch.randint(-100, 100, (n, n), device=dev, dtype=torch.int8).t()   # column-major B, as cuBLASLt wants
+        out["int8_tops"] = best(lambda: torch._int_mm(a8, b8))
+    except Exception as e:
+        out["int8_tops"], out["int8_error"] = None, f"{type(e).__name__}: {e}"[:160]
+    try:
+        af = torch.randn(n, n, device=dev).to(torch.float8_e4m3fn)
+        bf = torch.randn(n, n, device=dev).to(torch.float8_e4m3fn).t()
+        one = torch.ones((), device=dev, dtype=torch.float32)
+        out["fp8_tflops"] = best(lambda: torch._scaled_mm(af, bf, scale_a=one, scale_b=one, out_dtype=torch.bfloat16))
+    except Exception as e:
+        out["fp8_tflops"], out["fp8_error"] = None, f"{type(e).__name__}: {e}"[:160]
+    return out
+
+
+def mixed_ceiling(qk_peak, pv_peak):
+    """Half of the attention flops run as QK^T (one tensor rate), half as P.V (another): the time-weighted
+    ceiling is the harmonic combination."""
+    if not qk_peak or not pv_peak:
+        return None
+    return 2.0 / (1.0 / qk_peak + 1.0 / pv_peak)
+
+
+def run_sweep(dev, sampler, ceilings, reps=5):
+    """The metric's whole range in one run: hd {64,128} x {full, causal} x N {1K..32K} x PV {fp8, f16}, B=4 H=32
+    (protocol of /root/reference/bench/bench_qk_int8_pv_fp8_cuda.py:70-98: random INT8 Q/K codes, random scales;
+    kernel-only = the attention launch alone, median of `reps` CUDA-event timings of single launches through the
+    C ABI).  `op_tops` = the WHOLE OPERATOR through the public Python API on fp16/bf16 q, k, v (quantisation
+    pre-pass + kernel + host cost of the call: back-to-back API calls, no CUDA-graph replay).  Every entry carries
+    the SM clock samples taken while it ran."""
+    import torch
+    import sageattention_b200 as sb
+    from sageattention_b200 import core
+    B, H = 4, 32
+    out = []
+    g = torch.Generator(device=dev).manual_seed(0)
+
+    def timed(fn, n_rep):
+        evs = []
+        for _ in range(n_rep):
+            a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b_.record()
+            evs.append((a, b_))
+        torch.cuda.synchronize()
+        ts = sorted(a.elapsed_time(b_) for a, b_ in evs)
+        return ts[len(ts) // 2]
+
+    for d in (128, 64):
+        for n in (1024, 2048, 4096, 8192, 16384, 32768):
+            q8 = torch.randint(-95, 95, (B, H, n, d), dtype=torch.int8, device=dev, generator=g)
+            k8 = torch.randint(-95, 95, (B, H, n, d), dtype=torch.int8, device=dev, generator=g)
+            qs = torch.rand(B, H, (n + 127) // 128 * 32, device=dev, generator=g) * 0.01 + 0.005
+            ks = torch.rand(B, H, (n + 63) // 64 * 4, device=dev, generator=g) * 0.01 + 0.005
+            v16 = torch.randn(B, H, n, d, device=dev, generator=g).to(torch.float16)
+            v8 = torch.randn(B, H, d, (n + 127) // 128 * 128, device=dev, generator=g).to(torch.float8_e4m3fn)
+            vs = torch.rand(B, H, d, device=dev, generator=g) + 0.5
+            o = torch.empty(B, H, n, d, dtype=torch.float16, device=dev)
+            qf = torch.randn(B, H, n, d, device=dev, generator=g).to(torch.float16)
+            kf = torch.randn(B, H, n, d, device=dev, generator=g).to(torch.float16)
+            sm = d ** -0.5
+            for causal in (False, True):
+                flops = flops_of(B, H, n, d, causal)
+                for pv in ("fp8", "f16"):
+                    fp8 = pv == "fp8"
+                    kern = lambda: core._launch(fp8, q8, k8, v8 if fp8 else v16, o, qs, ks, vs if fp8 else None, None,
+                                                "HND", causal, 3, 32, sm, False)
+                    api = sb.sageattn_qk_int8_pv_fp8_cuda if fp8 else sb.sageattn_qk_int8_pv_fp16_cuda
+                    op = lambda: api(qf, kf, v16, is_causal=causal)
+                    n_rep = reps if n >= 8192 else 4 * reps
+                    for _ in range(3):
+                        kern()
+                        op()
+                    torch.cuda.synchronize()
+                    t0 = time.monotonic()
+                    k_ms = timed(kern, n_rep)
+                    # the operator: n_rep back-to-back API calls between two events (what a caller's loop sees)
+                    a, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    a.record()
+                    for _ in range(n_rep):
+                        op()
+                    b_.record()
+                    torch.cuda.synchronize()
+                    op_ms = a.elapsed_time(b_) / n_rep
+                    t1 = time.monotonic()
+                    ck = sampler.window(t0, t1) if sampler is not None else None
+                    pv_peak = ceilings.get("fp8_tflops") if fp8 else ceilings.get("bf16_tflops")
+                    ceil = mixed_ceiling(ceilings.get("int8_tops"), pv_peak)
+                    k_tops = flops / (k_ms * 1e-3) * 1e-12
+                    out.append({"hd": d, "n": n, "causal": causal, "pv": pv, "kernel_ms": round(k_ms, 4),
+                                "kernel_tops": round(k_tops, 1), "op_ms": round(op_ms, 4),
+                                "op_tops": round(flops / (op_ms * 1e-3) * 1e-12, 1),
+                                "frac_of_measured_ceiling": round(k_tops / ceil, 4) if ceil else None,
+                                "clocks": ck})
+            del q8, k8, qs, ks, v16, v8, vs, o, qf, kf
+            torch.cuda.empty_cache()
+    return out
+
+
+def run_sp(dev, world, rank, barrier, max_over_ranks, transport="nccl", reps=5):
+    """The sequence-parallel DiT record (BASELINE.json config 5): one Wan2.1-14B attention layer, B1 H40 N75600 hd128
+    bf16, through `sageattn`.  World 1: the layer on one GPU.  World P: activations sharded along the sequence
+    ([1, N/P, H, D] per rank), `ulysses_sageattn` = all-to-all in (scatter heads, gather sequence), attention on H/P
+    heads of the full sequence, all-to-all out; `comm_ms` = the same call with a null attention function, i.e. the
+    two all-to-alls and the gather / interleave copies alone; `one_gpu_ms` = the whole layer timed on rank 0's GPU in
+    this same run, `efficiency` = one_gpu_ms / (P * ms).  Device time, max over ranks, barrier on both sides."""
+    import torch
+    import sageattention_b200 as sb
+    from sageattention_b200 import parallel
+    b, h, n, d = 1, 40, 75600, 128
+    flops = flops_of(b, h, n, d, False)
+    g = torch.Generator(device=dev).manual_seed(100 + rank)
+
+    def timed(fn):
+        for _ in range(3):
+            fn()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1) / reps)
+
+    q, k, v = (torch.randn(b, h, n, d, device=dev, generator=g).to(torch.bfloat16) for _ in range(3))
+    one_ms = timed(lambda: sb.sageattn(q, k, v, tensor_layout="HND", is_causal=False))
+    rec = {"layer": f"Wan2.1-14B attention layer: sageattn B={b} H={h} N={n} D={d} bfloat16 non-causal",
+           "one_gpu_ms": round(one_ms, 3), "one_gpu_tops": round(flops / (one_ms * 1e-3) * 1e-12, 1)}
+    del q, k, v
+    if world == 1:
+        rec.update({"mode": "single GPU", "ms": rec["one_gpu_ms"], "tops": rec["one_gpu_tops"], "comm_ms": 0.0,
+                    "efficiency": 1.0})
+        return rec
+    assert h % world == 0 and n % world == 0
+    n_loc = n // world
+    qs, ks_, vs_ = (torch.randn(b, n_loc, h, d, device=dev, generator=g).to(torch.bfloat16) for _ in range(3))
+    full = lambda: parallel.ulysses_sageattn(qs, ks_, vs_, attn_fn=sb.sageattn, transport=transport, is_causal=False)
+    null_attn = lambda q_, k_, v_, **kw: torch.empty_like(q_)
+    comm = lambda: parallel.ulysses_sageattn(qs, ks_, vs_, attn_fn=null_attn, transport=transport, is_causal=False)
+    ms = timed(full)
+    comm_ms = timed(comm)
+    rec.update({"mode": f"Ulysses all-to-all ({transport}) over {world} GPUs, sequence shard {n_loc} tokens per rank",
+                "ms": round(ms, 3), "tops": round(flops / (ms * 1e-3) * 1e-12, 1), "comm_ms": round(comm_ms, 3),
+                "efficiency": round(one_ms / (world * ms), 4),
+                "a2a_bytes_per_rank": int(4 * b * n_loc * h * d * 2 * (world - 1) / world)})
+    return rec
 
 
 def cpu_sample(api, b, h, n, d, causal, dtype_name, budget_s=20.0):
@@ -177,7 +374,7 @@ def run_reference(args):
         "steps": len(tops_l), "warmup": args.warmup, "ms_per_step": statistics.mean(ts) * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8+fp16" if "fp16" in api else "int8+fp8",
         "data": "synthetic",
-        "config": {"workload": f"{args.workload}: {api} B={b} H={h} N={n} D={d} causal={causal} {dtype_name}"},
+        "config": {"workload": workload_string(args.workload)},
         "cpu_baseline": {"value": val, "unit": "TOPS", "cores": os.cpu_count(), "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "TOPS", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "the reference has no CPU implementation of this path; this is the CPU restatement (oracle/) of its algorithm",
@@ -192,7 +389,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2_fp16", choices=sorted(WORKLOADS))
-    ap.add_argument("--no-sweep", action="store_true")
+    ap.add_argument("--no-sweep", action="store_true", help="skip the hd x mask x N x PV sweep (N=1 only) in the line")
+    ap.add_argument("--no-sp", action="store_true", help="skip the sequence-parallel Wan layer record")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--sp", default="heads", choices=["heads", "ulysses"],
                     help="DiT workloads under torchrun: head sharding (no collective) or Ulysses all-to-all")
@@ -289,7 +487,7 @@ def main():
     kern_ms = [a.elapsed_time(bb) for a, bb in core.KERNEL_EVENTS]
     core.KERNEL_EVENTS = None
     kern_ms_avg = max_over_ranks(sum(kern_ms) / len(kern_ms))
-    clocks = sampler.stop(t_begin, t_end) if rank == 0 else None
+    clocks = sampler.window(t_begin, t_end) if rank == 0 else None
     value = flops_job / (t_ms * 1e-3) * 1e-12
 
     # ---------------- end to end with host buffers
@@ -319,15 +517,27 @@ def main():
     e2e_ms = max_over_ranks(e0.elapsed_time(e1)) / ke
     e2e_val = flops_job / (e2e_ms * 1e-3) * 1e-12
     nbytes = q.numel() * q.element_size()
+    del pipe, qh, kh, vh, oh, ohs
+    sp = None
+    if not args.no_sp and not sharded:
+        del q, k, v, o
+        torch.cuda.empty_cache()
+        try:
+            sp = run_sp(dev, world, rank, barrier, max_over_ranks, transport=args.sp_transport)
+        except Exception as e:  # the headline line must survive a failure here
+            sp = {"error": f"{type(e).__name__}: {e}"[:300]}
 
     if rank != 0:
+        sampler.stop()
         if world > 1:
             dist.barrier()
             dist.destroy_process_group()
         return
 
     bf16_peak, hbm_peak, basis = peaks()
+    ceilings = measure_ceilings(dev)
     fp8 = "fp16_cuda" not in api
+    ceil_meas = mixed_ceiling(ceilings.get("int8_tops"), ceilings.get("fp8_tflops") if fp8 else ceilings.get("bf16_tflops"))
     mix = 2.0 if fp8 else 4.0 / 3.0
     peak = bf16_peak * mix
     achieved = flops_rank / (kern_ms_avg * 1e-3) * 1e-12
@@ -335,21 +545,33 @@ def main():
         "metric": METRIC, "value": value, "unit": "TOPS", "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": t_ms, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
         "dtype": "int8+fp8" if fp8 else "int8+fp16", "data": "synthetic",
-        "config": {"workload": f"{args.workload}: {api} B={b} H={h} N={n} D={d} causal={causal} {dtype_name}, "
-                               f"heads per rank {h_loc}" + (f", Ulysses all-to-all ({args.sp_transport}), {args.sp_chunks} head group(s) pipelined" if ulysses else ""),
+        "config": {"workload": workload_string(args.workload), "heads_per_rank": h_loc,
+                   "split": (f"Ulysses all-to-all ({args.sp_transport}), {args.sp_chunks} head group(s) pipelined" if ulysses
+                             else ("heads across ranks, no collective" if sharded else "independent replicas per rank, no collective")),
                    "l2": "inputs+outputs per step (%.0f MB) exceed the 126 MB L2" % (4 * nbytes / 1e6)},
         "e2e": {"value": e2e_val, "unit": "TOPS", "h2d_bytes_per_step": 3 * nbytes * world,
                 "d2h_bytes_per_step": nbytes * world, "ms_per_step": e2e_ms},
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s",
-                     "frac": achieved / peak, "traffic": NCU_TRAFFIC.get(args.workload), "kernel": "sage_attn_fwd_kernel",
+                     "frac": achieved / peak, "traffic": NCU_TRAFFIC.get(args.workload),
+                     "traffic_source": NCU_TRAFFIC_SOURCE.get(args.workload), "kernel": "sage_attn_fwd_kernel",
                      "kernel_ms": kern_ms_avg,
                      "peak_basis": f"{basis} bf16 cuBLAS {bf16_peak:.0f} TF/s x {mix:.3f} (i8/fp8 MMAs run at 2x the f16 rate); "
                                    f"nominal {'4500' if fp8 else '3000'}",
-                     "frac_of_nominal": achieved / (4500.0 if fp8 else 3000.0)},
+                     "frac_of_nominal": achieved / (4500.0 if fp8 else 3000.0),
+                     "measured_ceilings": ceilings, "peak_from_measured_int8_and_pv_gemm": ceil_meas,
+                     "frac_of_measured_int8_and_pv_gemm": (achieved / ceil_meas) if ceil_meas else None},
         "kernel_only_tops": achieved,
     }
+    if sp is not None:
+        line["sp"] = sp
+    if world == 1 and not args.no_sweep:
+        try:
+            line["sweep"] = run_sweep(dev, sampler, ceilings)
+        except Exception as e:
+            line["sweep"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+    sampler.stop()
     if not args.no_cpu and world == 1:
         ctops, sample, _ = cpu_sample(api, b, h, n, d, causal, dtype_name)
         line["cpu_baseline"] = {"value": ctops, "unit": "TOPS", "cores": os.cpu_count(), "kind": "port",

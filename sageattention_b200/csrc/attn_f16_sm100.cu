@@ -42,8 +42,11 @@ using namespace sage;
 #ifndef SAGE_MAXTREE
 #define SAGE_MAXTREE 0
 #endif
+// f16 conversions issued group by group (16 columns) inside the exp phase, under the MUFU pipe (see attn_sm100.cu).
+// Measured at hd128 N=8192: 1183 (median; 1252 best, noisy) -> 1263 TOPS (stable); the e4m3 / head_dim-64 kernels
+// lose 2-5 % with it (quarter-rate F2FP.E4M3 lengthens their alternating exp window), so it is on here only.
 #ifndef SAGE_FUSE
-#define SAGE_FUSE 0
+#define SAGE_FUSE 1
 #endif
 
 template <int D, bool kFp8>
