@@ -275,7 +275,7 @@ def run_sweep(dev, sampler, ceilings, reps=5):
     return out
 
 
-def run_sp(dev, world, rank, barrier, max_over_ranks, transport="nccl", reps=5):
+def run_sp(dev, world, rank, barrier, max_over_ranks, transport="nccl", chunks=1, comm_sms=0, reps=5):
     """The sequence-parallel DiT record (BASELINE.json config 5): one Wan2.1-14B attention layer, B1 H40 N75600 hd128
     bf16, through `sageattn`.  World 1: the layer on one GPU.  World P: activations sharded along the sequence
     ([1, N/P, H, D] per rank), `ulysses_sageattn` = all-to-all in (scatter heads, gather sequence), attention on H/P
@@ -313,12 +313,14 @@ def run_sp(dev, world, rank, barrier, max_over_ranks, transport="nccl", reps=5):
     assert h % world == 0 and n % world == 0
     n_loc = n // world
     qs, ks_, vs_ = (torch.randn(b, n_loc, h, d, device=dev, generator=g).to(torch.bfloat16) for _ in range(3))
-    full = lambda: parallel.ulysses_sageattn(qs, ks_, vs_, attn_fn=sb.sageattn, transport=transport, is_causal=False)
+    full = lambda: parallel.ulysses_sageattn(qs, ks_, vs_, attn_fn=sb.sageattn, transport=transport, head_chunks=chunks,
+                                             comm_sms=comm_sms, is_causal=False)
     null_attn = lambda q_, k_, v_, **kw: torch.empty_like(q_)
     comm = lambda: parallel.ulysses_sageattn(qs, ks_, vs_, attn_fn=null_attn, transport=transport, is_causal=False)
     ms = timed(full)
     comm_ms = timed(comm)
-    rec.update({"mode": f"Ulysses all-to-all ({transport}) over {world} GPUs, sequence shard {n_loc} tokens per rank",
+    rec.update({"mode": f"Ulysses all-to-all ({transport}) over {world} GPUs, sequence shard {n_loc} tokens per rank, "
+                        f"{chunks} head group(s) pipelined, {comm_sms} SMs left to the collective",
                 "ms": round(ms, 3), "tops": round(flops / (ms * 1e-3) * 1e-12, 1), "comm_ms": round(comm_ms, 3),
                 "efficiency": round(one_ms / (world * ms), 4),
                 "a2a_bytes_per_rank": int(4 * b * n_loc * h * d * 2 * (world - 1) / world)})
@@ -396,6 +398,8 @@ def main():
                     help="DiT workloads under torchrun: head sharding (no collective) or Ulysses all-to-all")
     ap.add_argument("--sp-chunks", type=int, default=1,
                     help="Ulysses: groups of heads whose all-to-alls overlap the attention of another group")
+    ap.add_argument("--sp-comm-sms", type=int, default=0,
+                    help="Ulysses with --sp-chunks > 1: SMs the attention grid leaves free for the NCCL kernels")
     ap.add_argument("--sp-transport", default="nccl", choices=["nccl", "p2p"],
                     help="Ulysses: NCCL all-to-all, or copy-engine pushes into the peers' symmetric memory")
     args = ap.parse_args()
@@ -523,7 +527,8 @@ def main():
         del q, k, v, o
         torch.cuda.empty_cache()
         try:
-            sp = run_sp(dev, world, rank, barrier, max_over_ranks, transport=args.sp_transport)
+            sp = run_sp(dev, world, rank, barrier, max_over_ranks, transport=args.sp_transport, chunks=args.sp_chunks,
+                        comm_sms=args.sp_comm_sms)
         except Exception as e:  # the headline line must survive a failure here
             sp = {"error": f"{type(e).__name__}: {e}"[:300]}
 

@@ -159,6 +159,8 @@ typedef struct sage_attn_args {
   void* debug_s;   /* NULL, or int32 [B,Hq,ceil256(Nq),128]: raw QK^T of kv tile 0 (test hook) */
   int d_og;        /* 0 = D, else the real head_dim (multiple of 8, <= D) of o and of an f16 v: their rows hold
                       d_og elements; TMA zero-fills / clips the columns up to D (no F.pad, no output slice) */
+  int max_ctas;    /* 0 = one CTA per SM; else an upper bound on the persistent grid, so that a concurrent kernel
+                      on another stream (an NCCL collective under sequence parallelism) finds free SMs */
 } sage_attn_args;
 
 int sage_attn_i8_f16(const sage_attn_args* a, void* stream);

@@ -28,7 +28,7 @@ class AttnArgs(ctypes.Structure):
         ("q_scale", c_vp), ("k_scale", c_vp), ("v_scale", c_vp), ("v_mean", c_vp), ("lse", c_vp),
         ("B", c_int), ("Hq", c_int), ("Hkv", c_int), ("Nq", c_int), ("Nk", c_int), ("D", c_int),
         ("npad_v", c_int), ("gran", c_int), ("warp_q", c_int), ("is_causal", c_int),
-        ("out_dtype", c_int), ("sm_scale", c_f32), ("debug_s", c_vp), ("d_og", c_int),
+        ("out_dtype", c_int), ("sm_scale", c_f32), ("debug_s", c_vp), ("d_og", c_int), ("max_ctas", c_int),
     ]
 
 

@@ -24,6 +24,11 @@ _LOG2E = 1.44269504
 # launch (the roofline's "dominant kernel" duration); None = no events recorded.
 KERNEL_EVENTS = None
 
+# Upper bound on the attention kernel's persistent grid (None = one CTA per SM).  parallel.ulysses_sageattn sets
+# it while head groups are pipelined, so that the NCCL all-to-all of one group finds free SMs next to the
+# attention of another (sage_attn_args.max_ctas).
+GRID_LIMIT = None
+
 
 def _pad_head_dim(q, k, v):
     """Zero-pad head_dim to 64 / 128 like core.py:590-601."""
@@ -117,6 +122,7 @@ def _launch(fp8, q_int8, k_int8, v, o, q_scale, k_scale, v_scale, v_mean, tensor
     a.sm_scale = float(sm_scale)
     a.debug_s = debug_s.data_ptr() if debug_s is not None else None
     a.d_og = o.size(-1) if o.size(-1) != d else 0
+    a.max_ctas = int(GRID_LIMIT) if GRID_LIMIT else 0
     fn = lib.sage_attn_i8_f8 if fp8 else lib.sage_attn_i8_f16
     with _on_device(o.device):
         if KERNEL_EVENTS is not None:

@@ -585,7 +585,9 @@ static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
   p.sched_counter = acquire_sched_counter(stream);
   if (p.sched_counter == nullptr) return -1;
   SAGE_CUDA(cudaMemsetAsync(p.sched_counter, 0, sizeof(unsigned int), stream));
-  const int grid = (int)(n_work < sm_count() ? n_work : sm_count());
+  int ctas = sm_count();
+  if (a->max_ctas > 0 && a->max_ctas < ctas) ctas = a->max_ctas;
+  const int grid = (int)(n_work < ctas ? n_work : ctas);
   kern<<<grid, kThreads, L::kDynamic, stream>>>(tmQ, tmK, tmV, tmO, p);
   SAGE_CUDA(cudaGetLastError());
   return 0;

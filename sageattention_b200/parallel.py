@@ -239,7 +239,7 @@ def _ulysses_b1_p2p(q, k, v, group, world, attn_fn, head_chunks, kwargs):
 
 def ulysses_sageattn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, group=None,
                      attn_fn: Optional[Callable] = None, head_chunks: int = 1, transport: str = "nccl",
-                     **kwargs) -> torch.Tensor:
+                     comm_sms: int = 0, **kwargs) -> torch.Tensor:
     """Sequence-parallel attention.  q, k, v: this rank's sequence block, "NHD" layout
     [B, N/P, H, D] (all ranks hold equally long blocks; pad the sequence to a multiple of P first).
     Returns this rank's block of the output, [B, N/P, H, D].  kwargs go to the attention function
@@ -248,7 +248,9 @@ def ulysses_sageattn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, group=No
     the peers' symmetric-memory arenas by the copy engines, which (unlike NCCL's kernels) run under the
     persistent attention grid of another head group.
     `head_chunks`: with B = 1, how many groups the rank's heads are split into so that the all-to-alls of
-    one group overlap the attention of another (1 = no overlap)."""
+    one group overlap the attention of another (1 = no overlap).
+    `comm_sms`: with head_chunks > 1 and NCCL, how many SMs the persistent attention grid leaves free, so that
+    NCCL's all-to-all kernels (which need SMs) really run next to the attention of another group."""
     if kwargs.pop("return_lse", False):
         raise ValueError("ulysses_sageattn does not return the LSE")
     kwargs.pop("tensor_layout", None)
@@ -267,6 +269,14 @@ def ulysses_sageattn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, group=No
                 raise ValueError("transport='p2p' needs CUDA tensors")
             return _ulysses_b1_p2p(q, k, v, group if group is not None else dist.group.WORLD, world, attn_fn,
                                    head_chunks, kwargs)
+        if comm_sms > 0 and head_chunks > 1 and q.is_cuda:
+            from . import core
+            sms = torch.cuda.get_device_properties(q.device).multi_processor_count
+            prev, core.GRID_LIMIT = core.GRID_LIMIT, max(1, sms - comm_sms)
+            try:
+                return _ulysses_b1(q, k, v, group, world, attn_fn, head_chunks, kwargs)
+            finally:
+                core.GRID_LIMIT = prev
         return _ulysses_b1(q, k, v, group, world, attn_fn, head_chunks, kwargs)
     if k.size(2) == h and k.shape == q.shape:
         qkv = _seq_to_head_shard(torch.stack((q, k, v)), group, world)  # one collective for all three
