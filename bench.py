@@ -41,6 +41,7 @@ if ROOT not in sys.path:
 WORKLOADS = {
     # name: (api, B, H, N, D, causal, dtype)
     "c2_fp16": ("sageattn_qk_int8_pv_fp16_cuda", 4, 32, 4096, 128, False, "float16"),
+    "c2_fp16_bf16in": ("sageattn_qk_int8_pv_fp16_cuda", 4, 32, 4096, 128, False, "bfloat16"),
     "c3_fp8": ("sageattn_qk_int8_pv_fp8_cuda", 4, 32, 4096, 128, False, "float16"),
     "c3_fp8_8k": ("sageattn_qk_int8_pv_fp8_cuda", 4, 32, 8192, 128, False, "bfloat16"),
     "hunyuan": ("sageattn", 1, 24, 119056, 128, False, "bfloat16"),

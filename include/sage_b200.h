@@ -113,6 +113,16 @@ int sage_prepass_qk_int8(sage_tensor4 q, sage_tensor4 k, sage_tensor4 q_out, sag
                          int Nk, int D, int dtype, int per_thread, int warp_q, int q_scale_per_bh,
                          int k_scale_per_bh, int d_og, void* stream);
 
+/* sage_prepass_qk_int8 plus, from the same launch, v16 = half(v): the f16 copy the f16-P.V operator makes of a
+ * bf16 V (/root/reference/sageattention/core.py:633 `v.to(torch.float16)`, a separate eager kernel there and in
+ * round 1 here).  v: [B,Hkv,Nk,d_og] in the layout of k; v16_out: same shape, f16, rows 16-byte aligned.  Codes,
+ * scales and mean are bit-identical to sage_prepass_qk_int8; v16 is bit-identical to the torch cast. */
+int sage_prepass_qk_int8_v16(sage_tensor4 q, sage_tensor4 k, sage_tensor4 q_out, sage_tensor4 k_out,
+                             float* q_scale, float* k_scale, void* k_mean_out, sage_tensor4 v,
+                             sage_tensor4 v16_out, int B, int Hq, int Hkv, int Nq, int Nk, int D, int dtype,
+                             int per_thread, int warp_q, int q_scale_per_bh, int k_scale_per_bh, int d_og,
+                             void* stream);
+
 /* The Q/K/V prologue of the fp8-P.V operator (no smooth_v) in one launch: what sage_prepass_qk_int8(q, k) and
  * sage_per_channel_fp8(v, smooth_v = 0) produce, bit for bit (same arguments; v is [B,Hkv,Nk,D], n_stat as for
  * sage_per_channel_fp8, no workspace needed). */

@@ -46,6 +46,8 @@ SIGNATURES = {
     "sage_smooth_quant_k_int8": (c_int, [Tensor4, c_vp, Tensor4, c_vp, c_int, c_int, c_int, c_int, c_int,
                                          c_int, c_int, c_vp]),
     "sage_prepass_qk_int8": (c_int, [Tensor4, Tensor4, Tensor4, Tensor4, c_vp, c_vp, c_vp] + [c_int] * 12 + [c_vp]),
+    "sage_prepass_qk_int8_v16": (c_int, [Tensor4, Tensor4, Tensor4, Tensor4, c_vp, c_vp, c_vp, Tensor4, Tensor4]
+                                 + [c_int] * 12 + [c_vp]),
     "sage_prepass_qkv_fp8": (c_int, [Tensor4, Tensor4, Tensor4, Tensor4, c_vp, c_vp, c_vp, Tensor4, c_vp, c_i64, c_i64,
                                      c_i64, c_vp] + [c_int] * 12 + [c_f32, c_int, c_vp]),
     "sage_sub_mean": (c_int, [Tensor4, c_vp, Tensor4, c_int, c_int, c_int, c_int, c_int, c_vp]),
@@ -62,7 +64,7 @@ _lib = None
 # bumped on every call so bench.py can report how many of OUR kernels ran in its timed region.
 KERNELS_PER_CALL = {
     "sage_seq_mean": 1, "sage_seq_mean_static": 1, "sage_quant_int8": 1, "sage_quant_per_thread_int8": 1, "sage_sub_mean": 1,
-    "sage_smooth_quant_k_int8": 1, "sage_prepass_qk_int8": 1, "sage_prepass_qkv_fp8": 1,
+    "sage_smooth_quant_k_int8": 1, "sage_prepass_qk_int8": 1, "sage_prepass_qk_int8_v16": 1, "sage_prepass_qkv_fp8": 1,
     # smooth_v: statistics + conversion; otherwise one cluster launch
     "sage_per_channel_fp8": (lambda a: 2 if a[14] else 1),
     "sage_attn_i8_f16": 1, "sage_attn_i8_f8": 1,

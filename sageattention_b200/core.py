@@ -71,18 +71,21 @@ def _fold_padding(head_dim, smooth_k, smooth_v):
     return head_dim not in (64, 128) and head_dim <= 128 and head_dim % 8 == 0 and smooth_k and not smooth_v
 
 
-def _quantize_qk(q, k, smooth_k, qk_quant_gran, tensor_layout, warp_q, return_lse, fold=False):
+def _quantize_qk(q, k, smooth_k, qk_quant_gran, tensor_layout, warp_q, return_lse, fold=False, v_to_f16=None):
     """The quantisation prologue (core.py:611-632): Q codes, and for K either the fused
     mean + quantise launch (smooth_k) or the plain quantiser.  Returns the four quantiser outputs
-    and the LSE correction (None unless smooth_k and return_lse)."""
+    and the LSE correction (None unless smooth_k and return_lse).
+    `v_to_f16` (smooth_k only): a bf16 V whose f16 copy (core.py:633) the same launch writes; it is then
+    returned as a sixth element."""
     if smooth_k:
         # one cluster-launched grid for the whole prologue: K slices (mean + quantise, K read once
         # from HBM) and Q tiles side by side (measured at C2: per_thread 105 us against 41 + 72 us as
         # two launches, per_warp 89 us against 45 + 62 us)
-        q_int8, q_scale, k_int8, k_scale, km = prepass_qk_int8(q, k, qk_quant_gran, WARPQ=warp_q,
-                                                                 tensor_layout=tensor_layout, _pad_head_dim=fold)
-        return q_int8, q_scale, k_int8, k_scale, (_lse_correction(q, km[..., :q.size(-1)], tensor_layout)
-                                                    if return_lse else None)
+        out = prepass_qk_int8(q, k, qk_quant_gran, WARPQ=warp_q, tensor_layout=tensor_layout, _pad_head_dim=fold,
+                              v=v_to_f16)
+        q_int8, q_scale, k_int8, k_scale, km = out[:5]
+        corr = _lse_correction(q, km[..., :q.size(-1)], tensor_layout) if return_lse else None
+        return (q_int8, q_scale, k_int8, k_scale, corr) + tuple(out[5:])
     if qk_quant_gran == "per_warp":
         out = per_warp_int8(q, k, None, tensor_layout=tensor_layout, BLKQ=128, WARPQ=warp_q, BLKK=64)
     else:
@@ -184,13 +187,18 @@ def sageattn_qk_int8_pv_fp16_cuda(
     if sm_scale is None:
         sm_scale = head_dim_og ** -0.5
     warp_q = 16 if (head_dim_og > 64 and pv_accum_dtype == "fp16+fp32") else 32
-    q_int8, q_scale, k_int8, k_scale, lse_correction = _quantize_qk(q, k, smooth_k, qk_quant_gran, tensor_layout,
-                                                                    warp_q, return_lse, fold)
+    # a bf16 V needs an f16 copy (core.py:633): on the default path it comes out of the prologue launch
+    fuse_v = smooth_k and not smooth_v and v.dtype == torch.bfloat16 and v.shape == k.shape
+    qk = _quantize_qk(q, k, smooth_k, qk_quant_gran, tensor_layout, warp_q, return_lse, fold,
+                      v_to_f16=v if fuse_v else None)
+    q_int8, q_scale, k_int8, k_scale, lse_correction = qk[:5]
     o = torch.empty(q.size(), dtype=dtype, device=q.device)
     v_mean = None
     if smooth_v:
         v16, vm = sub_mean(v, tensor_layout=tensor_layout)
         v_mean = vm.to(torch.float32)
+    elif fuse_v:
+        v16 = qk[5]
     else:
         v16 = v.to(torch.float16)
     gran = _lib.GRAN_PER_THREAD if qk_quant_gran == "per_thread" else _lib.GRAN_PER_WARP

@@ -191,10 +191,12 @@ def _padded_head_dim(d: int) -> int:
     return 64 if d <= 64 else 128
 
 
-def prepass_qk_int8(q, k, qk_quant_gran="per_thread", WARPQ=32, tensor_layout="HND", _pad_head_dim=False):
+def prepass_qk_int8(q, k, qk_quant_gran="per_thread", WARPQ=32, tensor_layout="HND", _pad_head_dim=False, v=None):
     """The operator's Q/K prologue with smooth_k in ONE launch (core.py:611-632): km = k.mean(seq),
     K codes/scales for that mean and Q codes/scales.  Returns (q_int8, q_scale, k_int8, k_scale, km),
-    identical to quant_q_int8(q) + smooth_quant_k_int8(k)."""
+    identical to quant_q_int8(q) + smooth_quant_k_int8(k).
+    With `v` (same heads / length as k): the same launch also writes v16 = v.to(float16) (core.py:633) and the
+    return value gains it as a sixth element."""
     _require_cuda(q, k)
     lib = _lib.load()
     b, hq, nq, d_og, q4 = _dims(q, tensor_layout)
@@ -214,6 +216,18 @@ def prepass_qk_int8(q, k, qk_quant_gran="per_thread", WARPQ=32, tensor_layout="H
         (b, hq, q_per_bh), dtype=torch.float32, device=q.device)
     k_scale = torch.empty((b, hk, k_per_bh), dtype=torch.float32, device=q.device)
     km = torch.empty((b, hk, d), dtype=k.dtype, device=k.device)
+    if v is not None:
+        _require_cuda(v)
+        _, hv, nv, dv, v4 = _dims(v, tensor_layout)
+        if (hv, nv, dv) != (hk, nk, d_og) or v.dtype != k.dtype:
+            raise ValueError("k and v must have the same heads, length, head_dim and dtype")
+        v16 = torch.empty(v.shape, dtype=torch.float16, device=v.device)
+        _, _, _, _, vo4 = _dims(v16, tensor_layout)
+        with _on_device(q.device):
+            _lib.check(lib.sage_prepass_qk_int8_v16(q4, k4, qo4, ko4, q_scale.data_ptr(), k_scale.data_ptr(),
+                                                    km.data_ptr(), v4, vo4, b, hq, hk, nq, nk, d, _dtype_code(q),
+                                                    per_thread, WARPQ, q_per_bh, k_per_bh, d_og, _stream(q)))
+        return q_int8, q_scale, k_int8, k_scale, km, v16
     with _on_device(q.device):
         _lib.check(lib.sage_prepass_qk_int8(q4, k4, qo4, ko4, q_scale.data_ptr(), k_scale.data_ptr(), km.data_ptr(),
                                             b, hq, hk, nq, nk, d, _dtype_code(q), per_thread, WARPQ, q_per_bh,
