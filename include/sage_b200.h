@@ -171,6 +171,12 @@ typedef struct sage_attn_args {
                       d_og elements; TMA zero-fills / clips the columns up to D (no F.pad, no output slice) */
   int max_ctas;    /* 0 = one CTA per SM; else an upper bound on the persistent grid, so that a concurrent kernel
                       on another stream (an NCCL collective under sequence parallelism) finds free SMs */
+  const void* mask;  /* NULL, or attn_mask [B|1, H|1, Nq, Lpad] (Lpad >= ceil128(Nk), the padding is never used; broadcast
+                        dims have stride 0; rows 16-byte aligned).  Reference: sageattn_qk_int8_pv_fp16_triton's attn_mask,
+                        /root/reference/sageattention/core.py:249-251, triton/attn_qk_int8_per_thread.py:39-72.  Not with is_causal. */
+  int mask_kind;     /* 1: bool as uint8 (non-zero = attend); 2 / 3: f16 / bf16, ADDED to the base-2 logits as it is (the
+                        reference does not scale it by log2 e) */
+  int64_t mask_stride_b, mask_stride_h, mask_stride_m; /* in elements */
 } sage_attn_args;
 
 int sage_attn_i8_f16(const sage_attn_args* a, void* stream);

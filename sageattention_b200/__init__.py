@@ -3,7 +3,8 @@
 Exports the same names as /root/reference/sageattention/__init__.py, as real distinct functions
 (the fork aliases them all to one implementation, __init__.py:59-95).
 """
-from .core import sageattn, sageattn_qk_int8_pv_fp16_cuda, sageattn_qk_int8_pv_fp8_cuda, sageattn_varlen
+from .core import (sageattn, sageattn_qk_int8_pv_fp16_cuda, sageattn_qk_int8_pv_fp16_triton, sageattn_qk_int8_pv_fp8_cuda,
+                   sageattn_varlen)
 from .host import HostPipeline
 from .parallel import shard_heads, ulysses_sageattn
 from .quant import (per_block_int8, per_channel_fp8, per_thread_int8, per_warp_int8, prepass_qk_int8, prepass_qkv_fp8, quant_q_int8, seq_mean,
@@ -16,6 +17,7 @@ sageattn_qk_int8_pv_fp8_cuda_sm90 = sageattn_qk_int8_pv_fp8_cuda
 __all__ = [
     "sageattn",
     "sageattn_qk_int8_pv_fp16_cuda",
+    "sageattn_qk_int8_pv_fp16_triton",
     "sageattn_qk_int8_pv_fp8_cuda",
     "sageattn_qk_int8_pv_fp8_cuda_sm90",
     "sageattn_varlen",

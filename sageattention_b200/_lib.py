@@ -29,6 +29,7 @@ class AttnArgs(ctypes.Structure):
         ("B", c_int), ("Hq", c_int), ("Hkv", c_int), ("Nq", c_int), ("Nk", c_int), ("D", c_int),
         ("npad_v", c_int), ("gran", c_int), ("warp_q", c_int), ("is_causal", c_int),
         ("out_dtype", c_int), ("sm_scale", c_f32), ("debug_s", c_vp), ("d_og", c_int), ("max_ctas", c_int),
+        ("mask", c_vp), ("mask_kind", c_int), ("mask_stride_b", c_i64), ("mask_stride_h", c_i64), ("mask_stride_m", c_i64),
     ]
 
 

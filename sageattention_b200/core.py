@@ -93,8 +93,43 @@ def _quantize_qk(q, k, smooth_k, qk_quant_gran, tensor_layout, warp_q, return_ls
     return (*out, None)
 
 
+def _prepare_mask(attn_mask, q, b, hq, nq, nk):
+    """attn_mask (bool, or q's dtype; broadcastable to [B, H, Nq, Nk] - core.py:249-251, 306-318) in the form the
+    kernels read: 4-D, batch / head dims of size 1 kept as stride-0 broadcasts, rows of ceil128(Nk) elements, 16-byte
+    aligned.  A mask that already has that form is used in place; otherwise ONE padded copy is made (of the
+    un-broadcast mask: a [1, 1, Nq, Nk] mask is copied once, not B*H times)."""
+    assert attn_mask.dtype == torch.bool or attn_mask.dtype == q.dtype, \
+        "attn_mask must be of dtype bool or the same dtype as q."
+    assert attn_mask.device == q.device, "All tensors must be on the same device."
+    m = attn_mask
+    while m.dim() < 4:
+        m = m.unsqueeze(0)
+    target = (b, hq, nq, nk)
+    try:
+        torch.broadcast_shapes(tuple(m.shape), target)
+        ok = all(ms in (1, ts) for ms, ts in zip(m.shape, target)) and m.dim() == 4
+    except RuntimeError:
+        ok = False
+    if not ok:
+        raise AssertionError(f"attn_mask shape {tuple(attn_mask.shape)} cannot be broadcast to {target}")
+    if m.size(2) == 1 or m.size(3) == 1:   # broadcast along the sequence dims: materialise those (small dims stay)
+        m = m.expand(m.size(0), m.size(1), nq, nk)
+    npad = (nk + 127) // 128 * 128
+    esz = 1 if m.dtype == torch.bool else 2
+    aligned = (m.stride(3) == 1 and m.stride(2) >= npad and (m.stride(2) * esz) % 16 == 0 and m.data_ptr() % 16 == 0
+               and all(m.size(i) == 1 or (m.stride(i) * esz) % 16 == 0 for i in (0, 1)))
+    if not aligned:
+        buf = torch.zeros((m.size(0), m.size(1), nq, npad), dtype=m.dtype, device=m.device)
+        buf[..., :nk].copy_(m)
+        m = buf
+    kind = 1 if m.dtype == torch.bool else (2 if m.dtype == torch.float16 else 3)
+    sb = m.stride(0) if m.size(0) > 1 else 0
+    sh = m.stride(1) if m.size(1) > 1 else 0
+    return m, kind, sb, sh, m.stride(2)
+
+
 def _launch(fp8, q_int8, k_int8, v, o, q_scale, k_scale, v_scale, v_mean, tensor_layout, is_causal, gran,
-            warp_q, sm_scale, return_lse, npad_v=0, debug_s=None):
+            warp_q, sm_scale, return_lse, npad_v=0, debug_s=None, mask=None):
     """One call into sage_attn_i8_f8 / sage_attn_i8_f16; returns the base-2 LSE or None."""
     lib = _lib.load()
     b, hq, nq, d, q4 = _dims(q_int8, tensor_layout)
@@ -126,6 +161,9 @@ def _launch(fp8, q_int8, k_int8, v, o, q_scale, k_scale, v_scale, v_mean, tensor
     a.debug_s = debug_s.data_ptr() if debug_s is not None else None
     a.d_og = o.size(-1) if o.size(-1) != d else 0
     a.max_ctas = int(GRID_LIMIT) if GRID_LIMIT else 0
+    if mask is not None:
+        mt, a.mask_kind, a.mask_stride_b, a.mask_stride_h, a.mask_stride_m = mask
+        a.mask = mt.data_ptr()
     fn = lib.sage_attn_i8_f8 if fp8 else lib.sage_attn_i8_f16
     with _on_device(o.device):
         if KERNEL_EVENTS is not None:
@@ -288,6 +326,59 @@ def sageattn(
     return sageattn_qk_int8_pv_fp8_cuda(q, k, v, tensor_layout=tensor_layout, is_causal=is_causal,
                                         sm_scale=sm_scale, pv_accum_dtype="fp32+fp32", smooth_k=smooth_k,
                                         return_lse=return_lse)
+
+
+@torch.compiler.disable
+def sageattn_qk_int8_pv_fp16_triton(
+    q: torch.Tensor,
+    k: torch.Tensor,
+    v: torch.Tensor,
+    tensor_layout: str = "HND",
+    quantization_backend: str = "triton",
+    is_causal: bool = False,
+    attn_mask: Optional[torch.Tensor] = None,
+    sm_scale: Optional[float] = None,
+    smooth_k: bool = True,
+    return_lse: bool = False,
+    **kwargs: Any,
+) -> torch.Tensor:
+    """The reference's Triton entry point (core.py:160-361; exported by its __init__ because diffusers imports it),
+    and the one that takes an `attn_mask`.  There is no Triton here: the call runs on the same sm_100a kernels as
+    sageattn_qk_int8_pv_fp16_cuda (INT8 QK^T with per-thread scales, f16 P.V, fp32 accumulation in TMEM).
+
+    attn_mask: bool (True = attend) or q's dtype (ADDED to the base-2 logits as it is - the reference does not scale
+    it by log2 e, triton/attn_qk_int8_per_thread.py:68-72), broadcastable to [B, H, Nq, Nk]; not with is_causal.
+    Masked keys contribute exactly 0; a query row with every key masked gives zeros (the reference's finite -1e6
+    leaves an unmasked softmax over the partially masked blocks there, SDPA gives NaN).
+    quantization_backend ("triton" | "cuda") is accepted for compatibility; both use per-thread quantisation here
+    (the reference feeds per-thread or per-block scales to the same per-thread kernel, core.py:295-299)."""
+    dtype = q.dtype
+    assert q.is_cuda, "Input tensors must be on cuda."
+    assert dtype in [torch.float16, torch.bfloat16], \
+        "Input tensors must be in dtype of torch.float16 or torch.bfloat16"
+    assert q.device == k.device == v.device, "All tensors must be on the same device."
+    assert q.dtype == k.dtype == v.dtype, "All tensors must have the same dtype."
+    if quantization_backend not in ("triton", "cuda"):
+        raise ValueError(f"Unsupported quantization backend: {quantization_backend}")
+    if attn_mask is None:
+        return sageattn_qk_int8_pv_fp16_cuda(q, k, v, tensor_layout=tensor_layout, is_causal=is_causal,
+                                             qk_quant_gran="per_thread", sm_scale=sm_scale, pv_accum_dtype="fp32",
+                                             smooth_k=smooth_k, return_lse=return_lse)
+    assert not is_causal, "Mask should be None for causal attention."
+    head_dim_og = q.size(-1)
+    q, k, v = _pad_head_dim(q, k, v)
+    assert q.stride(-1) == 1 and k.stride(-1) == 1 and v.stride(-1) == 1, "Last dim of qkv must be contiguous."
+    if sm_scale is None:
+        sm_scale = head_dim_og ** -0.5
+    b, hq, nq, _, _ = _dims(q, tensor_layout)
+    _, _, nk, _, _ = _dims(k, tensor_layout)
+    mask = _prepare_mask(attn_mask, q, b, hq, nq, nk)
+    q_int8, q_scale, k_int8, k_scale, lse_correction = _quantize_qk(q, k, smooth_k, "per_thread", tensor_layout, 32,
+                                                                    return_lse)
+    o = torch.empty(q.size(), dtype=dtype, device=q.device)
+    lse = _launch(False, q_int8, k_int8, v.to(torch.float16), o, q_scale, k_scale, None, None, tensor_layout, False,
+                  _lib.GRAN_PER_THREAD, 32, sm_scale, return_lse, mask=mask)
+    return _finish(o, lse, lse_correction, sm_scale, head_dim_og, return_lse)
 
 
 @torch.compiler.disable

@@ -67,6 +67,11 @@ struct AttnKernelParams {
   unsigned int* sched_counter;  // zeroed on the launch stream just before the kernel; see g_sched_counter
   int out_bf16;
   float sm_scale_log2;
+  // attn_mask (kMask kernels only): [B|1, H|1, Nq, >= ceil128(Nk)] with broadcast dims at stride 0, rows 16-byte
+  // aligned and readable up to the end of the last kv tile; strides in elements
+  const uint8_t* mask;
+  int mask_kind;  // 0 none, 1 bool (u8, non-zero = attend), 2 f16 additive, 3 bf16 additive
+  long long mask_sb, mask_sh, mask_sm;
 };
 
 
@@ -161,6 +166,7 @@ struct ItemCtx {
   int q_row;
   float qs;        // q scale of the row (raw: the load is still in flight when setup returns)
   const float* ksp;
+  const uint8_t* mask_row;  // this row's attn_mask (kv column 0), kMask kernels only
 };
 template <int D>
 __device__ __forceinline__ ItemCtx softmax_setup(const AttnKernelParams& p, int t, int row,
@@ -173,6 +179,7 @@ __device__ __forceinline__ ItemCtx softmax_setup(const AttnKernelParams& p, int 
   c.q_row = 0;
   c.qs = 0.f;
   c.ksp = nullptr;
+  c.mask_row = nullptr;
   if (!c.valid) return c;
   int n_it[2];
   item_iters(p, wi.q_pair, n_it);
@@ -187,6 +194,10 @@ __device__ __forceinline__ ItemCtx softmax_setup(const AttnKernelParams& p, int 
     }
   }
   c.q_row = (wi.q_pair * 2 + t) * kTileQ + row;
+  if (p.mask != nullptr) {
+    const long long qr = min(c.q_row, p.Nq - 1);  // rows beyond Nq are computed and clipped: any valid row will do
+    c.mask_row = p.mask + (wi.b * p.mask_sb + wi.h * p.mask_sh + qr * p.mask_sm) * (p.mask_kind == 1 ? 1 : 2);
+  }
   {
     const int sh = (p.warp_q == 16) ? 4 : 5;
     int idx;
@@ -284,7 +295,7 @@ __device__ __forceinline__ void softmax_epilogue(const AttnKernelParams& p, int 
   ++st.items;
   tc_fence_after();
   SAGE_STAMP(t, st.steps - 1, 8);
-  const float inv_d = rcp_approx(d_run);
+  const float inv_d = (d_run > 0.f) ? rcp_approx(d_run) : 0.f;  // d = 0: every key of the row masked (attn_mask) -> zeros
   // The tile goes out through shared memory and ONE bulk tensor store per 64-column block (a thread
   // owns a row, so direct stores would be 16 bytes per thread at a row pitch: measured 5-7 k cycles
   // per item).  The previous item's store must have finished reading the staging tile first.
@@ -463,6 +474,17 @@ static int check_attn_args(const sage_attn_args* a) {
   SAGE_REQUIRE(a->o.stride_n % 8 == 0 && a->o.stride_h % 8 == 0 && a->o.stride_b % 8 == 0 &&
                (reinterpret_cast<uintptr_t>(a->o.ptr) & 15) == 0, "output rows must be 16-byte aligned");
   SAGE_REQUIRE(a->B <= 65535 && a->Hq <= 65535, "batch / heads exceed grid limits");
+  if (a->mask != nullptr) {
+    SAGE_REQUIRE(a->mask_kind >= 1 && a->mask_kind <= 3, "attn_mask kind must be 1 (bool), 2 (f16) or 3 (bf16), got %d", a->mask_kind);
+    SAGE_REQUIRE(!a->is_causal, "attn_mask must be null for causal attention");
+    const long long esz = a->mask_kind == 1 ? 1 : 2;
+    SAGE_REQUIRE((reinterpret_cast<uintptr_t>(a->mask) & 15) == 0 && (a->mask_stride_b * esz) % 16 == 0 &&
+                 (a->mask_stride_h * esz) % 16 == 0 && (a->mask_stride_m * esz) % 16 == 0,
+                 "attn_mask rows must be 16-byte aligned (pad the last dimension to a multiple of 128)");
+    SAGE_REQUIRE(a->mask_stride_m >= (a->Nk + 127) / 128 * 128,
+                 "attn_mask rows must hold ceil128(kv_len) = %d elements (got row stride %lld)", (a->Nk + 127) / 128 * 128,
+                 (long long)a->mask_stride_m);
+  }
   return 0;
 }
 

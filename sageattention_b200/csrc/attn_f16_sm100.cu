@@ -71,7 +71,7 @@ struct SmemLayout {
 };
 
 // The kv steps of one work item for Q tile `t` (128 threads, thread = query row).
-template <int D, bool kFp8>
+template <int D, bool kFp8, bool kMask>
 __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, int row,
                                               const ItemCtx& c, const WorkItem* ring, uint32_t it,
                                               uint32_t tmem_base, uint64_t* s_full, uint64_t* p_full,
@@ -91,7 +91,8 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
   // Only the first n_pingpong steps of an item, which both warpgroups execute, take part.  Warpgroup 1
   // grants warpgroup 0's first turn of an item either here or, when it can, right after its own last
   // exp phase of the previous item (so that warpgroup 0 does not wait for warpgroup 1's epilogue).
-  if (SAGE_TURN != 0 && t == 1 && n_pingpong > 0) {
+  constexpr int kTurn = kMask ? 0 : SAGE_TURN;
+  if (kTurn != 0 && t == 1 && n_pingpong > 0) {
     if (!st.granted) named_bar_arrive(1, 2 * kTileQ);
     st.granted = false;
   }
@@ -143,14 +144,22 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
     const bool masked_tile = (j == n_iter - 1) && (p.causal || (p.Nk - kv0) < kTileKV);
     float alpha, bias[8], dsum;
     uint32_t w[kFp8 ? 32 : 64];
-    if (masked_tile) softmax_max<kFp8, true, false>(s, sc, lim, m_run, alpha, bias);
+    if constexpr (kMask) {
+      // attn_mask: max, exponentials and row sum of y = logit + mask in one call (softmax_sm100.cuh)
+      dsum = softmax_general_mask<kFp8>(s, sc, lim, c.mask_row + (size_t)kv0 * (p.mask_kind == 1 ? 1 : 2), p.mask_kind,
+                                        m_run, alpha);
+    } else if (masked_tile) softmax_max<kFp8, true, false>(s, sc, lim, m_run, alpha, bias);
     else if (SAGE_MAXTREE) softmax_max_tree<kFp8>(s, sc, m_run, alpha, bias);
     else softmax_max<kFp8, false, false>(s, sc, 127, m_run, alpha, bias);
     SAGE_STAMP(t, st.steps, 5);
     // The exp phases of the two warpgroups alternate (they are the only MUFU-bound stretch): each
     // warpgroup's load / max / pack / store phases then run under the other one's exponentials.
-    if (SAGE_TURN == 1 && j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
+    if (kTurn == 1 && j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
     SAGE_STAMP(t, st.steps, 6);
+    constexpr int kFuse = kMask ? 0 : SAGE_FUSE;
+    if constexpr (kMask) {
+      // (exponentials done above)
+    } else {
 #if SAGE_FUSE
     // conversions issued group by group (16 columns) under the MUFU pipe; SAGE_FUSE == 2 also stores every group
     // over the consumed S columns as soon as it is packed
@@ -177,7 +186,8 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
     if (masked_tile) dsum = softmax_exp<true, 0, 128, 3, false>(s, sc, bias, lim);
     else dsum = softmax_exp<false, 0, 128, 3, false>(s, sc, bias, 127);
 #endif
-    if (SAGE_TURN == 1 && j < n_pingpong) {
+    }
+    if (kTurn == 1 && j < n_pingpong) {
       if (t == 0) {
         named_bar_arrive(2, 2 * kTileQ);
       } else if (j < n_pingpong - 1) {
@@ -189,9 +199,7 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
     }
     SAGE_STAMP(t, st.steps, 7);
     d_run = fmaf(d_run, alpha, dsum);
-#if !SAGE_FUSE
-    softmax_pack<kFp8>(s, w);
-#endif
+    if constexpr (kFuse == 0) softmax_pack<kFp8>(s, w);
     SAGE_STAMP(t, st.steps, 3);
     // rescale O when some row of this warp moved its max (PV(j-1) is complete: S(j) was issued after
     // it and tcgen05.commit tracks all earlier MMAs)
@@ -209,7 +217,7 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
       }
     }
     // P row -> TMEM, over the S columns just consumed
-    if (SAGE_FUSE == 2) {
+    if (kFuse == 2) {
       // (stored group by group inside the window)
     } else if constexpr (kFp8) {
       tmem_st32(tS, w);
@@ -231,7 +239,7 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
 }
 
 // ------------------------------------------------------------------------------------------
-template <int D, bool kFp8>
+template <int D, bool kFp8, bool kMask = false>
 __global__ void __launch_bounds__(kThreads, 1)
 sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                      const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
@@ -303,7 +311,7 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     while (c.valid) {
       float m_run = 0.f, d_run = 1.f;
       if (c.n_iter > 0)
-        softmax_steps<D, kFp8>(p, t, row, c, ring, it, tmem_base, s_full, p_full, st, m_run,
+        softmax_steps<D, kFp8, kMask>(p, t, row, c, ring, it, tmem_base, s_full, p_full, st, m_run,
                                d_run);
       // the next item is prepared under this item's last P.V
       const bool had_steps = c.n_iter > 0;
@@ -514,7 +522,7 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
 namespace sage_f16 {
 using namespace sage;
 
-template <int D, bool kFp8>
+template <int D, bool kFp8, bool kMask = false>
 static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
   using L = SmemLayout<D, kFp8>;
   CUtensorMap tmQ, tmK, tmV, tmO;
@@ -574,7 +582,11 @@ static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
   p.out_bf16 = (a->out_dtype == SAGE_DTYPE_BF16);
   p.sm_scale_log2 = a->sm_scale * 1.44269504088896340736f;
 
-  auto kern = sage_attn_fwd_kernel<D, kFp8>;
+  SAGE_REQUIRE(kMask == (a->mask != nullptr), "internal: mask kernel selection");
+  p.mask = reinterpret_cast<const uint8_t*>(a->mask);
+  p.mask_kind = a->mask_kind;
+  p.mask_sb = a->mask_stride_b; p.mask_sh = a->mask_stride_h; p.mask_sm = a->mask_stride_m;
+  auto kern = sage_attn_fwd_kernel<D, kFp8, kMask>;
   // per template instantiation AND per device: function attributes belong to the device's context
   static SmemAttrOnce smem_attr;
   SAGE_CUDA(smem_attr.ensure(kern, L::kDynamic));
@@ -609,6 +621,7 @@ extern "C" int sage_attn_i8_f16(const sage_attn_args* a, void* stream) {
   return a->D == 128 ? sage_f16::launch_attn<128, false>(a, s) : sage_f16::launch_attn<64, false>(a, s);
 #else
   // head_dim 64: TMEM has room for an un-aliased P, so the shared design of attn_sm100.cu is used
+  if (a->D == 128 && a->mask != nullptr) return sage_f16::launch_attn<128, false, true>(a, s);
   return a->D == 128 ? sage_f16::launch_attn<128, false>(a, s) : sage::launch_attn_f16_d64(a, s);
 #endif
 }

@@ -96,7 +96,7 @@ struct SmemLayout {
 };
 
 // The kv steps of one work item for Q tile `t` (128 threads, thread = query row).
-template <int D, bool kFp8>
+template <int D, bool kFp8, bool kMask>
 __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, int row,
                                               const ItemCtx& c, const WorkItem* ring, uint32_t it,
                                               uint32_t tmem_base, uint8_t* p_smem, uint64_t* s_full,
@@ -117,7 +117,9 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
   // Only the first n_pingpong steps of an item, which both warpgroups execute, take part.  Warpgroup 1
   // grants warpgroup 0's first turn of an item either here or, when it can, right after its own last
   // exp phase of the previous item (so that warpgroup 0 does not wait for warpgroup 1's epilogue).
-  if (SAGE_TURN != 0 && t == 1 && n_pingpong > 0) {
+  // (the attn_mask kernels run their warpgroups freely: kTurn = 0)
+  constexpr int kTurn = kMask ? 0 : SAGE_TURN;
+  if (kTurn != 0 && t == 1 && n_pingpong > 0) {
     if (!st.granted) named_bar_arrive(1, 2 * kTileQ);
     st.granted = false;
   }
@@ -185,7 +187,11 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
     if (p.causal) lim = min(lim, q_row - kv0);
     const bool masked_tile = (j == n_iter - 1) && (p.causal || (p.Nk - kv0) < kTileKV);
     float alpha, bias[8], dsum;
-    if (masked_tile) softmax_max<kFp8, true, false>(s, sc, lim, m_run, alpha, bias);
+    if constexpr (kMask) {
+      // attn_mask: max, exponentials and row sum of y = logit + mask in one call (softmax_sm100.cuh)
+      dsum = softmax_general_mask<kFp8>(s, sc, lim, c.mask_row + (size_t)kv0 * (p.mask_kind == 1 ? 1 : 2), p.mask_kind,
+                                        m_run, alpha);
+    } else if (masked_tile) softmax_max<kFp8, true, false>(s, sc, lim, m_run, alpha, bias);
     else if (SAGE_MAXTREE) softmax_max_tree<kFp8>(s, sc, m_run, alpha, bias);
     else softmax_max<kFp8, false, false>(s, sc, 127, m_run, alpha, bias);
     SAGE_STAMP(t, st.steps, 5);
@@ -196,7 +202,7 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
 #if SAGE_FUSE
     // PV(j-1) complete: P tile reusable (checked before the window when the groups are stored inside it)
     if (SAGE_FUSE == 2 && j > 0) mbar_wait(&p_empty[t], ph ^ 1u);
-    if (SAGE_TURN == 1 && j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
+    if (kTurn == 1 && j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
     SAGE_STAMP(t, st.steps, 6);
     uint32_t w[kFp8 ? 32 : 64];  // (SAGE_FUSE == 2 reuses the first group's words)
     auto window = [&](auto masked_c) {
@@ -223,7 +229,7 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
     };
     if (masked_tile) window(std::true_type{});
     else window(std::false_type{});
-    if (SAGE_TURN == 1 && j < n_pingpong) {
+    if (kTurn == 1 && j < n_pingpong) {
       if (t == 0) {
         named_bar_arrive(2, 2 * kTileQ);
       } else if (j < n_pingpong - 1) {
@@ -241,11 +247,12 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
     uint32_t w[kFp8 ? 32 : 64];
     // The exp phases of the two warpgroups alternate (they are the only MUFU-bound stretch): each
     // warpgroup's load / max / pack / store phases then run under the other one's exponentials.
-    if (SAGE_TURN == 1 && j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
+    if (kTurn == 1 && j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
     SAGE_STAMP(t, st.steps, 6);
-    if (masked_tile) dsum = softmax_exp<true, 0, 128, 3, false>(s, sc, bias, lim);
+    if constexpr (kMask) { /* done above */ }
+    else if (masked_tile) dsum = softmax_exp<true, 0, 128, 3, false>(s, sc, bias, lim);
     else dsum = softmax_exp<false, 0, 128, 3, false>(s, sc, bias, 127);
-    if (SAGE_TURN == 1 && j < n_pingpong) {
+    if (kTurn == 1 && j < n_pingpong) {
       if (t == 0) {
         named_bar_arrive(2, 2 * kTileQ);
       } else if (j < n_pingpong - 1) {
@@ -325,7 +332,7 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
 }
 
 // ------------------------------------------------------------------------------------------
-template <int D, bool kFp8>
+template <int D, bool kFp8, bool kMask = false>
 __global__ void __launch_bounds__(kThreads, 1)
 sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                      const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
@@ -401,7 +408,7 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     while (c.valid) {
       float m_run = 0.f, d_run = 1.f;
       if (c.n_iter > 0)
-        softmax_steps<D, kFp8>(p, t, row, c, ring, it, tmem_base, smem + L::kPOff + t * L::kPBytes,
+        softmax_steps<D, kFp8, kMask>(p, t, row, c, ring, it, tmem_base, smem + L::kPOff + t * L::kPBytes,
                                s_full, s_free, p_full, p_empty, st, m_run, d_run);
       // the next item is prepared under this item's last P.V
       const bool had_steps = c.n_iter > 0;
@@ -628,7 +635,7 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
 // ==========================================================================================
 namespace sage {
 
-template <int D, bool kFp8>
+template <int D, bool kFp8, bool kMask = false>
 static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
   using L = SmemLayout<D, kFp8>;
   CUtensorMap tmQ, tmK, tmV, tmO;
@@ -688,7 +695,11 @@ static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
   p.out_bf16 = (a->out_dtype == SAGE_DTYPE_BF16);
   p.sm_scale_log2 = a->sm_scale * 1.44269504088896340736f;
 
-  auto kern = sage_attn_fwd_kernel<D, kFp8>;
+  SAGE_REQUIRE(kMask == (a->mask != nullptr), "internal: mask kernel selection");
+  p.mask = reinterpret_cast<const uint8_t*>(a->mask);
+  p.mask_kind = a->mask_kind;
+  p.mask_sb = a->mask_stride_b; p.mask_sh = a->mask_stride_h; p.mask_sm = a->mask_stride_m;
+  auto kern = sage_attn_fwd_kernel<D, kFp8, kMask>;
   // per template instantiation AND per device: function attributes belong to the device's context
   static SmemAttrOnce smem_attr;
   SAGE_CUDA(smem_attr.ensure(kern, L::kDynamic));
@@ -712,7 +723,9 @@ static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
 // head_dim 64 with f16 P also runs on this kernel (P in spare TMEM columns, S(j+1) issued as soon as
 // S(j) is drained); called from sage_attn_i8_f16 in attn_f16_sm100.cu
 namespace sage {
-int launch_attn_f16_d64(const sage_attn_args* a, cudaStream_t stream) { return launch_attn<64, false>(a, stream); }
+int launch_attn_f16_d64(const sage_attn_args* a, cudaStream_t stream) {
+  return a->mask ? launch_attn<64, false, true>(a, stream) : launch_attn<64, false>(a, stream);
+}
 }  // namespace sage
 
 #ifdef SAGE_TRACE
@@ -725,5 +738,7 @@ extern "C" int sage_attn_i8_f8(const sage_attn_args* a, void* stream) {
   int rc = sage::check_attn_args(a);
   if (rc) return rc;
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
+  if (a->mask != nullptr)
+    return a->D == 128 ? sage::launch_attn<128, true, true>(a, s) : sage::launch_attn<64, true, true>(a, s);
   return a->D == 128 ? sage::launch_attn<128, true>(a, s) : sage::launch_attn<64, true>(a, s);
 }

@@ -2,6 +2,7 @@
 // stand-alone softmax microbenchmark tools/softmax_bench.cu).
 #pragma once
 #include <cstdint>
+#include <cuda_fp16.h>
 #include "ptx_sm100.cuh"
 
 namespace sage {
@@ -219,6 +220,81 @@ __device__ __forceinline__ void softmax_exp_pack16(const int kG, uint32_t (&s)[1
     for (int i = 0; i < 8; ++i)
       w[i] = pack_f16x2(__uint_as_float(s[kG * 16 + 2 * i]), __uint_as_float(s[kG * 16 + 2 * i + 1]));
   }
+}
+
+// ------------------------------------------------------------------------------------------
+// General attention mask (attn_mask of sageattn_qk_int8_pv_fp16_triton, /root/reference/sageattention/core.py:249-251,
+// triton/attn_qk_int8_per_thread.py:39-72).  One path for both kinds, in the float domain:
+//   y[c] = s[c] * sc[class] + add[c],   add = 0 / -1e30 for a bool mask (True = attend), or the mask VALUE for a
+//   mask of q's dtype - added to the base-2 logits as it is, which is what the reference does (it does not scale
+//   the mask by log2 e); columns beyond `lim` (kv_len, as without a mask) count as masked.
+// Then the usual lazily-rescaled online softmax on y.  Masked entries contribute exactly 0; a row with nothing
+// left keeps m = -1e30, d = 0 (the epilogue writes zeros for it).
+// mrow_ptr: the row's mask for THIS kv tile (128 readable elements, 16-byte aligned).  kind: 1 u8 bool, 2 f16, 3 bf16.
+__device__ __forceinline__ uint4 ldg_nc_v4(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.v4.u32 {%0, %1, %2, %3}, [%4];\n" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+template <bool kFp8>
+__device__ __forceinline__ float softmax_general_mask(uint32_t (&s)[128], const float (&sc)[8], int lim,
+                                                      const uint8_t* mrow_ptr, int kind, float& m_run, float& alpha) {
+  constexpr float kNeg = -1e30f;
+  float mrow = kNeg;
+  // pass A: y = dequantised logit + mask, in place (float bits), running maximum
+#pragma unroll
+  for (int c0 = 0; c0 < 128; c0 += 16) {
+    float add[16];
+    if (kind == 1) {
+      const uint4 w = ldg_nc_v4(mrow_ptr + c0);
+      const uint32_t ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+      for (int i = 0; i < 16; ++i) add[i] = ((ww[i >> 2] >> (8 * (i & 3))) & 0xffu) ? 0.f : kNeg;
+    } else {
+      const uint4 w0 = ldg_nc_v4(mrow_ptr + (size_t)c0 * 2), w1 = ldg_nc_v4(mrow_ptr + (size_t)c0 * 2 + 16);
+      const uint32_t ww[8] = {w0.x, w0.y, w0.z, w0.w, w1.x, w1.y, w1.z, w1.w};
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        const uint32_t h16 = (ww[i >> 1] >> (16 * (i & 1))) & 0xffffu;
+        float f;
+        if (kind == 2) f = __half2float(__ushort_as_half((unsigned short)h16));
+        else f = __uint_as_float(h16 << 16);
+        add[i] = fmaxf(f, kNeg);   // -inf (and NaN) -> -1e30: masked
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      const int c = c0 + i;
+      const float x = __int_as_float((int)s[c] + kMagicI);
+      float y = fmaf(x, sc[kcls(c)], -kMagicF * sc[kcls(c)]) + add[i];
+      y = (c > lim || add[i] <= kNeg) ? kNeg : y;
+      s[c] = __float_as_uint(y);
+      mrow = fmaxf(mrow, y);
+    }
+  }
+  const bool grow = mrow > m_run + (kFp8 ? kFp8Tau : kF16Tau);
+  float m_new = m_run;
+  alpha = 1.0f;
+  if (__any_sync(0xffffffffu, grow)) {
+    m_new = fmaxf(m_run, mrow);
+    alpha = ex2_approx(m_run - m_new);  // 0 on the first unmasked tile (m_run = -1e30)
+  }
+  m_run = m_new;
+  // pass B: p = 2^(y - m [+ offset]); a masked y = -1e30 gives exactly 0 (also while m is still -1e30: the
+  // argument is clamped so that -1e30 - (-1e30) does not read as 0)
+  const float off = (kFp8 ? kFp8Offset : 0.f) - m_new;
+  float d0 = 0.f, d1 = 0.f;
+#pragma unroll
+  for (int c = 0; c < 128; c += 2) {
+    const float y0 = __uint_as_float(s[c]), y1 = __uint_as_float(s[c + 1]);
+    const float p0 = (y0 <= kNeg) ? 0.f : ex2_approx(y0 + off);
+    const float p1 = (y1 <= kNeg) ? 0.f : ex2_approx(y1 + off);
+    d0 += p0;
+    d1 += p1;
+    s[c] = __float_as_uint(p0);
+    s[c + 1] = __float_as_uint(p1);
+  }
+  return d0 + d1;
 }
 
 // Phase 3: pack p to e4m3 (32 words) / f16 (64 words).
