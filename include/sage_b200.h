@@ -59,6 +59,21 @@ size_t sage_seq_mean_workspace_bytes(int B, int H, int N, int D);
 int sage_seq_mean(sage_tensor4 x, void* out, int B, int H, int N, int D, int dtype, void* workspace,
                   void* stream);
 
+/* Packed variable-length batches (sageattn_varlen): per-block INT8 quantisation of q [Tq,Hq,D] (pre-scaled by
+ * sm_scale_q = sm_scale * log2 e) and k [Tk,Hkv,D] (minus km [Hkv,D] when km != NULL) in ONE launch, bit-identical to
+ * the reference's Triton kernel (/root/reference/sageattention/triton/quant_per_block_varlen.py:20-107): blocks of 128
+ * (q) / 64 (k) rows restarting at every sequence, scale = amax / 127 with no floor, round half away from zero.
+ * q_scale / k_scale: [blocks, H] like the reference's, sequence b starting at row cu_seqlens_*_scale[b]; those prefix
+ * arrays [nseq+1] and cu_pairs [nseq+1] (prefix of ceil(q_len/256), the attention kernel's work list) are OUTPUTS of
+ * this launch.  The caller sizes the scale buffers for the upper bound ceil(T/BLK) + nseq rows: no length is needed on
+ * the host.  Strides in elements; outputs contiguous. */
+int sage_quant_per_block_varlen_int8(const void* q, const void* k, const void* km, int8_t* q_out, int8_t* k_out,
+                                     float* q_scale, float* k_scale, const int* cu_seqlens_q, const int* cu_seqlens_k,
+                                     int* cu_seqlens_q_scale, int* cu_seqlens_k_scale, int* cu_pairs, int nseq, int Hq,
+                                     int Hkv, int D, int dtype, int max_seqlen_q, int max_seqlen_k, int64_t q_stride_n,
+                                     int64_t q_stride_h, int64_t k_stride_n, int64_t k_stride_h, float sm_scale_q,
+                                     void* stream);
+
 /* sage_seq_mean without a workspace argument and without any allocation.
  * NO COUNTERPART IN THE REFERENCE: added for callers that cannot call
  * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  Same arithmetic and
@@ -177,6 +192,14 @@ typedef struct sage_attn_args {
   int mask_kind;     /* 1: bool as uint8 (non-zero = attend); 2 / 3: f16 / bf16, ADDED to the base-2 logits as it is (the
                         reference does not scale it by log2 e) */
   int64_t mask_stride_b, mask_stride_h, mask_stride_m; /* in elements */
+  /* Packed variable-length batches (sageattn_varlen, /root/reference/sageattention/core.py:363-477; f16 P.V only).
+     NULL cu_seqlens_q = fixed-length call.  Otherwise q8 / k8 / v / o are [tokens, H, D] passed as B = 1, Nq / Nk = the
+     token counts, gran = SAGE_GRAN_PER_BLOCK; the five int32 device arrays [nseq + 1] are the caller's cu_seqlens and
+     the outputs of sage_quant_per_block_varlen_int8; q_scale / k_scale are its [blocks, H] scale arrays.  ONE launch
+     covers the pack: the persistent work list is derived from cu_pairs on the device (no length is read by the host). */
+  const int* cu_seqlens_q; const int* cu_seqlens_k; const int* cu_seqlens_q_scale; const int* cu_seqlens_k_scale;
+  const int* cu_pairs;
+  int nseq;
 } sage_attn_args;
 
 int sage_attn_i8_f16(const sage_attn_args* a, void* stream);

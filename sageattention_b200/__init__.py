@@ -7,7 +7,7 @@ from .core import (sageattn, sageattn_qk_int8_pv_fp16_cuda, sageattn_qk_int8_pv_
                    sageattn_varlen)
 from .host import HostPipeline
 from .parallel import shard_heads, ulysses_sageattn
-from .quant import (per_block_int8, per_channel_fp8, per_thread_int8, per_warp_int8, prepass_qk_int8, prepass_qkv_fp8, quant_q_int8, seq_mean,
+from .quant import (per_block_int8, per_block_int8_varlen, per_channel_fp8, per_thread_int8, per_warp_int8, prepass_qk_int8, prepass_qkv_fp8, quant_q_int8, seq_mean,
                     smooth_quant_k_int8, sub_mean)
 
 # the reference's sm90 entry point has the same contract as the fp8 one; on sm_100a both are the
@@ -22,6 +22,7 @@ __all__ = [
     "sageattn_qk_int8_pv_fp8_cuda_sm90",
     "sageattn_varlen",
     "per_block_int8",
+    "per_block_int8_varlen",
     "per_warp_int8",
     "per_thread_int8",
     "sub_mean",

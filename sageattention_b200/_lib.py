@@ -30,6 +30,8 @@ class AttnArgs(ctypes.Structure):
         ("npad_v", c_int), ("gran", c_int), ("warp_q", c_int), ("is_causal", c_int),
         ("out_dtype", c_int), ("sm_scale", c_f32), ("debug_s", c_vp), ("d_og", c_int), ("max_ctas", c_int),
         ("mask", c_vp), ("mask_kind", c_int), ("mask_stride_b", c_i64), ("mask_stride_h", c_i64), ("mask_stride_m", c_i64),
+        ("cu_seqlens_q", c_vp), ("cu_seqlens_k", c_vp), ("cu_seqlens_q_scale", c_vp), ("cu_seqlens_k_scale", c_vp),
+        ("cu_pairs", c_vp), ("nseq", c_int),
     ]
 
 
@@ -40,6 +42,7 @@ SIGNATURES = {
     "sage_seq_mean_workspace_bytes": (ctypes.c_size_t, [c_int] * 4),
     "sage_seq_mean": (c_int, [Tensor4, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp]),
     "sage_seq_mean_static": (c_int, [Tensor4, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp]),
+    "sage_quant_per_block_varlen_int8": (c_int, [c_vp] * 12 + [c_int] * 7 + [c_i64] * 4 + [c_f32, c_vp]),
     "sage_quant_int8": (c_int, [Tensor4, c_vp, Tensor4, c_vp, c_int, c_int, c_int, c_int, c_int, c_int,
                                 c_int, c_int, c_f32, c_vp]),
     "sage_quant_per_thread_int8": (c_int, [Tensor4, c_vp, Tensor4, c_vp, c_int, c_int, c_int, c_int, c_int,
@@ -64,7 +67,7 @@ _lib = None
 # kernels launched by one call of each entry point (cudaMemsetAsync is not counted); LAUNCHES is
 # bumped on every call so bench.py can report how many of OUR kernels ran in its timed region.
 KERNELS_PER_CALL = {
-    "sage_seq_mean": 1, "sage_seq_mean_static": 1, "sage_quant_int8": 1, "sage_quant_per_thread_int8": 1, "sage_sub_mean": 1,
+    "sage_seq_mean": 1, "sage_seq_mean_static": 1, "sage_quant_per_block_varlen_int8": 1, "sage_quant_int8": 1, "sage_quant_per_thread_int8": 1, "sage_sub_mean": 1,
     "sage_smooth_quant_k_int8": 1, "sage_prepass_qk_int8": 1, "sage_prepass_qk_int8_v16": 1, "sage_prepass_qkv_fp8": 1,
     # smooth_v: statistics + conversion; otherwise one cluster launch
     "sage_per_channel_fp8": (lambda a: 2 if a[14] else 1),

@@ -14,7 +14,8 @@ from typing import Any, Optional
 import torch
 
 from . import _lib
-from .quant import (_dims, _dtype_code, _on_device, _require_cuda, _stream, per_block_int8, per_channel_fp8, per_thread_int8,
+from .quant import (_dims, _dtype_code, _on_device, _require_cuda, _stream, per_block_int8, per_block_int8_varlen, per_channel_fp8,
+                    per_thread_int8,
                     per_warp_int8, prepass_qk_int8, prepass_qkv_fp8, quant_q_int8, seq_mean, smooth_quant_k_int8,
                     sub_mean)
 
@@ -129,7 +130,7 @@ def _prepare_mask(attn_mask, q, b, hq, nq, nk):
 
 
 def _launch(fp8, q_int8, k_int8, v, o, q_scale, k_scale, v_scale, v_mean, tensor_layout, is_causal, gran,
-            warp_q, sm_scale, return_lse, npad_v=0, debug_s=None, mask=None):
+            warp_q, sm_scale, return_lse, npad_v=0, debug_s=None, mask=None, varlen=None):
     """One call into sage_attn_i8_f8 / sage_attn_i8_f16; returns the base-2 LSE or None."""
     lib = _lib.load()
     b, hq, nq, d, q4 = _dims(q_int8, tensor_layout)
@@ -164,6 +165,11 @@ def _launch(fp8, q_int8, k_int8, v, o, q_scale, k_scale, v_scale, v_mean, tensor
     if mask is not None:
         mt, a.mask_kind, a.mask_stride_b, a.mask_stride_h, a.mask_stride_m = mask
         a.mask = mt.data_ptr()
+    if varlen is not None:
+        cu_q, cu_k, cu_qs, cu_ks, cu_pairs = varlen
+        a.cu_seqlens_q, a.cu_seqlens_k = cu_q.data_ptr(), cu_k.data_ptr()
+        a.cu_seqlens_q_scale, a.cu_seqlens_k_scale, a.cu_pairs = cu_qs.data_ptr(), cu_ks.data_ptr(), cu_pairs.data_ptr()
+        a.nseq = cu_q.numel() - 1
     fn = lib.sage_attn_i8_f8 if fp8 else lib.sage_attn_i8_f16
     with _on_device(o.device):
         if KERNEL_EVENTS is not None:
@@ -398,14 +404,12 @@ def sageattn_varlen(
     """Packed variable-length batches (reference core.py:363-477): q [Tq, Hq, D], k / v [Tk, Hkv, D],
     cu_seqlens_* [batch + 1]; returns [Tq, Hq, D].
 
-    Same scheme as the reference: K is smoothed by its mean over ALL tokens of the pack (core.py:462),
-    Q/K are quantised per block (128 / 64 rows, Q pre-scaled by sm_scale * log2 e, blocks restart at every
-    sequence as in triton/quant_per_block_varlen.py:60), V is fp16, P.V accumulates in fp32.  First version
-    of this entry point: every sequence runs through the fixed-length sm_100a kernels on
-    views of the packed tensors (per-block quantiser launch + attention launch per sequence, output written
-    in place into the packed result), so it costs one host synchronisation for the sequence lengths and
-    3 launches per sequence - or 3 launches in all when every sequence of the pack has the same lengths (the
-    pack is then viewed as a [B, n, H, D] batch); a single-launch work list over cu_seqlens is the next step."""
+    Same scheme as the reference: K is smoothed by its mean over ALL tokens of the pack (core.py:462), Q / K are
+    quantised per block (128 / 64 rows, Q pre-scaled by sm_scale * log2 e, blocks restarting at every sequence) with
+    the arithmetic of the reference's Triton quantiser bit for bit (quant.per_block_int8_varlen), V is f16, P.V
+    accumulates in fp32.  Three launches for the whole pack whatever its make-up - the pack-wide K mean, ONE quantiser
+    launch for Q and K, ONE attention launch whose persistent work list is derived from cu_seqlens on the device - and
+    no host synchronisation: the call can be captured in a CUDA graph."""
     dtype = q.dtype
     assert q.is_cuda, "Input tensors must be on cuda."
     assert dtype in [torch.float16, torch.bfloat16], \
@@ -421,34 +425,20 @@ def sageattn_varlen(
     assert cu_seqlens_q.numel() == cu_seqlens_k.numel() and cu_seqlens_q.numel() >= 2
     if sm_scale is None:
         sm_scale = head_dim_og ** -0.5
-    v16 = v.to(torch.float16)
-    if smooth_k:
-        k = k - k.mean(dim=0, keepdim=True)  # over all sequences of the pack, in the input dtype (core.py:462-463)
-    # one device-to-host copy for both length vectors (the only host synchronisation of the call)
-    bq, bk = torch.stack((cu_seqlens_q.to(torch.int64), cu_seqlens_k.to(torch.int64))).tolist()
-    assert bq[-1] == q.size(0) and bk[-1] == k.size(0), "cu_seqlens do not cover the packed tensors"
+    tq, hq, d = q.shape
+    tk, hk, _ = k.shape
     o = torch.empty(q.shape, dtype=dtype, device=q.device)
-    nb = len(bq) - 1
-    lq, lk = bq[1] - bq[0], bk[1] - bk[0]
-    if kwargs.get("_batched", True) and nb > 1 and lq > 0 and lk > 0 and \
-            all(bq[i + 1] - bq[i] == lq and bk[i + 1] - bk[i] == lk for i in range(nb)):
-        # every sequence has the same lengths: the pack IS a [B, n, H, D] batch - one quantiser launch per
-        # tensor and one attention launch for all of it (same tiles, same bits as the per-sequence launches)
-        ranges = [(0, q.size(0), 0, k.size(0), nb)]
-    else:
-        ranges = [(bq[i], bq[i + 1], bk[i], bk[i + 1], 1) for i in range(nb)]
-    for q0, q1, k0, k1, nseq in ranges:
-        if q1 == q0:
-            continue
-        if k1 == k0:
-            o[q0:q1].zero_()
-            continue
-        assert (q1 - q0) // nseq <= max_seqlen_q and (k1 - k0) // nseq <= max_seqlen_k, "sequence longer than max_seqlen"
-        shp = lambda t, a, b_: t[a:b_].view(nseq, (b_ - a) // nseq, t.size(1), t.size(2))  # [B, n, H, D] "NHD" views
-        qi, ki, vi = shp(q, q0, q1), shp(k, k0, k1), shp(v16, k0, k1)
-        q_int8, q_scale, k_int8, k_scale = per_block_int8(qi, ki, None, BLKQ=128, BLKK=64, sm_scale=sm_scale,
-                                                          tensor_layout="NHD")
-        # Q already carries sm_scale * log2 e: the kernel's own factor must be 1
-        _launch(False, q_int8, k_int8, vi, shp(o, q0, q1), q_scale, k_scale, None, None, "NHD", is_causal,
-                _lib.GRAN_PER_BLOCK, 32, 1.0 / 1.44269504088896340736, False)
+    if tq == 0:
+        return o[..., :head_dim_og]
+    if tk == 0:
+        return o.zero_()[..., :head_dim_og]
+    v16 = v.to(torch.float16)
+    # mean over all sequences of the pack, in the input dtype (core.py:462); the subtraction happens in the quantiser
+    km = seq_mean(k.unsqueeze(0), tensor_layout="NHD") if smooth_k else None
+    q_int8, q_scale, k_int8, k_scale, cu_qs, cu_ks, (cu_q, cu_k, cu_pairs) = per_block_int8_varlen(
+        q, k, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, sm_scale=sm_scale, km=km)
+    # Q already carries sm_scale * log2 e: the kernel's own factor must be 1
+    _launch(False, q_int8.unsqueeze(0), k_int8.unsqueeze(0), v16.unsqueeze(0), o.unsqueeze(0), q_scale, k_scale, None, None,
+            "NHD", is_causal, _lib.GRAN_PER_BLOCK, 32, 1.0 / 1.44269504088896340736, False,
+            varlen=(cu_q, cu_k, cu_qs, cu_ks, cu_pairs))
     return o[..., :head_dim_og]

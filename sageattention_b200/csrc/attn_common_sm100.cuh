@@ -72,7 +72,26 @@ struct AttnKernelParams {
   const uint8_t* mask;
   int mask_kind;  // 0 none, 1 bool (u8, non-zero = attend), 2 f16 additive, 3 bf16 additive
   long long mask_sb, mask_sh, mask_sm;
+  // packed variable-length batches (kVarlen kernels, sageattn_varlen): q / k / v / o are [tokens, H, D] (B = 1 in the
+  // tensor maps), a work item's batch index is the SEQUENCE, scales are [blocks, H] with sequence s starting at row
+  // cu_*_scale[s], cu_pairs = prefix of ceil(q_len / 256) (all written by sage_quant_per_block_varlen_int8)
+  const int* cu_q; const int* cu_k; const int* cu_q_scale; const int* cu_k_scale; const int* cu_pairs;
+  int nseq;
 };
+
+// Token offsets and lengths of the sequence a work item belongs to (the whole tensor when not packed).
+struct SeqInfo { int q_off, q_len, k_off, k_len; };
+template <bool kVarlen>
+__device__ __forceinline__ SeqInfo seq_info(const AttnKernelParams& p, int b) {
+  SeqInfo si;
+  if constexpr (kVarlen) {
+    si.q_off = __ldg(p.cu_q + b); si.q_len = __ldg(p.cu_q + b + 1) - si.q_off;
+    si.k_off = __ldg(p.cu_k + b); si.k_len = __ldg(p.cu_k + b + 1) - si.k_off;
+  } else {
+    si.q_off = 0; si.q_len = p.Nq; si.k_off = 0; si.k_len = p.Nk;
+  }
+  return si;
+}
 
 
 // ---------------------------------------------------------------------------------------------
@@ -104,8 +123,30 @@ static __device__ unsigned int g_sched_counter[kSchedCounters];
 struct __align__(16) WorkItem {
   int q_pair, h, b, hkv;  // q_pair < 0: end of the list
 };
+template <bool kVarlen = false>
 __device__ __forceinline__ WorkItem decode_work(const AttnKernelParams& p, unsigned int w) {
   WorkItem o;
+  if constexpr (kVarlen) {
+    // head-major list over the pack's q pairs: w -> (h, global pair) -> (sequence, pair); the number of items is
+    // only known on the device
+    const int total = __ldg(p.cu_pairs + p.nseq);
+    if (total <= 0 || w >= (unsigned int)total * (unsigned int)p.Hq) {
+      o.q_pair = -1; o.h = 0; o.b = 0; o.hkv = 0;
+      return o;
+    }
+    const int h = (int)(w / (unsigned int)total);
+    const int pg = (int)w - h * total;
+    int lo = 0, hi = p.nseq;            // largest s with cu_pairs[s] <= pg
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (__ldg(p.cu_pairs + mid) <= pg) lo = mid; else hi = mid;
+    }
+    o.b = lo;
+    o.q_pair = pg - __ldg(p.cu_pairs + lo);
+    o.h = h;
+    o.hkv = h / (p.Hq / p.Hkv);
+    return o;
+  }
   if (w >= (unsigned int)p.n_work) {
     o.q_pair = -1; o.h = 0; o.b = 0; o.hkv = 0;
     return o;
@@ -139,13 +180,32 @@ __device__ __forceinline__ WorkItem read_work(const WorkItem* ring, uint64_t* sc
 }
 // kv tiles per q tile (causal: stop at the diagonal tile; top-left aligned as the reference,
 // /root/reference/csrc/qattn/qk_int_sv_f16_cuda_sm80.cu:218-222)
-__device__ __forceinline__ void item_iters(const AttnKernelParams& p, int q_pair, int (&n_it)[2]) {
+__device__ __forceinline__ void item_iters(const AttnKernelParams& p, int q_pair, int q_len, int k_len, int (&n_it)[2]) {
 #pragma unroll
   for (int t = 0; t < 2; ++t) {
     const int qs = (q_pair * 2 + t) * kTileQ;
-    int kv_end = p.Nk;
+    int kv_end = k_len;
     if (p.causal) kv_end = min(kv_end, qs + kTileQ);
-    n_it[t] = (qs < p.Nq) ? (kv_end + kTileKV - 1) / kTileKV : 0;
+    n_it[t] = (qs < q_len) ? (kv_end + kTileKV - 1) / kTileKV : 0;
+  }
+}
+__device__ __forceinline__ void item_iters(const AttnKernelParams& p, int q_pair, int (&n_it)[2]) {
+  item_iters(p, q_pair, p.Nq, p.Nk, n_it);
+}
+template <bool kVarlen>
+__device__ __forceinline__ void item_iters_of(const AttnKernelParams& p, const WorkItem& w, int (&n_it)[2]) {
+  if constexpr (kVarlen) {
+    const SeqInfo si = seq_info<true>(p, w.b);
+    item_iters(p, w.q_pair, si.q_len, si.k_len, n_it);
+    // a sequence with queries but no keys still takes ONE kv step, fully masked (lim = -1): P = 0, O = 0, d = 0 and
+    // the epilogue writes zeros, as the reference's kernel does (acc = 0, triton/attn_qk_int8_block_varlen.py) - and
+    // the pipeline's barriers, which advance per kv step, keep their protocol
+    if (si.k_len <= 0) {
+#pragma unroll
+      for (int t = 0; t < 2; ++t) n_it[t] = ((w.q_pair * 2 + t) * kTileQ < si.q_len) ? 1 : 0;
+    }
+  } else {
+    item_iters(p, w.q_pair, p.Nq, p.Nk, n_it);
   }
 }
 
@@ -167,8 +227,9 @@ struct ItemCtx {
   float qs;        // q scale of the row (raw: the load is still in flight when setup returns)
   const float* ksp;
   const uint8_t* mask_row;  // this row's attn_mask (kv column 0), kMask kernels only
+  int k_len, ks_stride, ks_count;  // kVarlen kernels: kv length of the sequence, stride / number of its k scales
 };
-template <int D>
+template <int D, bool kVarlen = false>
 __device__ __forceinline__ ItemCtx softmax_setup(const AttnKernelParams& p, int t, int row,
                                                  const WorkItem* ring, uint64_t* sched_full, uint32_t it) {
   ItemCtx c;
@@ -180,20 +241,33 @@ __device__ __forceinline__ ItemCtx softmax_setup(const AttnKernelParams& p, int 
   c.qs = 0.f;
   c.ksp = nullptr;
   c.mask_row = nullptr;
+  c.k_len = p.Nk; c.ks_stride = 1; c.ks_count = p.k_scale_per_bh;
   if (!c.valid) return c;
   int n_it[2];
-  item_iters(p, wi.q_pair, n_it);
+  item_iters_of<kVarlen>(p, wi, n_it);
   c.n_iter = n_it[t];
   c.n_pingpong = min(n_it[0], n_it[1]);
   {  // will both warpgroups alternate in the next item?  (the producer publishes one item ahead)
     const WorkItem nx = read_work(ring, sched_full, it + 1);
     if (nx.q_pair >= 0) {
       int n_nx[2];
-      item_iters(p, nx.q_pair, n_nx);
+      item_iters_of<kVarlen>(p, nx, n_nx);
       c.next_pingpong = min(n_nx[0], n_nx[1]) > 0;
     }
   }
-  c.q_row = (wi.q_pair * 2 + t) * kTileQ + row;
+  c.q_row = (wi.q_pair * 2 + t) * kTileQ + row;   // (kVarlen: row inside the sequence)
+  if constexpr (kVarlen) {
+    // per-block scales of this sequence: [blocks, H], block-major (quant_per_block_varlen.py:46)
+    const SeqInfo si = seq_info<true>(p, wi.b);
+    const int nqb = (si.q_len + 127) / 128;
+    const int tile = min(wi.q_pair * 2 + t, nqb - 1);
+    c.qs = __ldg(p.q_scale + (size_t)(__ldg(p.cu_q_scale + wi.b) + tile) * p.Hq + wi.h);
+    c.ksp = p.k_scale + (size_t)__ldg(p.cu_k_scale + wi.b) * p.Hkv + wi.hkv;
+    c.k_len = si.k_len;
+    c.ks_stride = p.Hkv;
+    c.ks_count = (si.k_len + 63) / 64;
+    return c;
+  }
   if (p.mask != nullptr) {
     const long long qr = min(c.q_row, p.Nq - 1);  // rows beyond Nq are computed and clipped: any valid row will do
     c.mask_row = p.mask + (wi.b * p.mask_sb + wi.h * p.mask_sh + qr * p.mask_sm) * (p.mask_kind == 1 ? 1 : 2);
@@ -270,7 +344,7 @@ __device__ __forceinline__ void epilogue_convert(const uint32_t (&o)[D], float i
 // Epilogue of one work item: O_t / d [* v_scale] [+ v_mean] -> 16-bit -> shared memory -> bulk tensor
 // store; LSE.  The issuer is already running the next item's Q.K^T under it; its first P.V (which
 // overwrites O_t) waits for this warpgroup's next P tile, i.e. for the loads done here.
-template <int D, bool kFp8>
+template <int D, bool kFp8, bool kVarlen = false>
 __device__ __forceinline__ void softmax_epilogue(const AttnKernelParams& p, int t, int row,
                                                  const WorkItem* ring, uint32_t it, uint32_t tmem_base,
                                                  uint8_t* o_smem, float* vs_smem, const CUtensorMap* tmO,
@@ -282,6 +356,13 @@ __device__ __forceinline__ void softmax_epilogue(const AttnKernelParams& p, int 
   const int h = wv.y, b = wv.z, hkv = wv.w;
   const int q_tile_start = (wv.x * 2 + t) * kTileQ;
   const int q_row = q_tile_start + row;
+  // kVarlen: the tile sits at token q_off + q_tile_start of the pack and may end inside the next sequence
+  int q_off = 0, rows_valid = kTileQ;
+  if constexpr (kVarlen) {
+    const SeqInfo si = seq_info<true>(p, b);
+    q_off = si.q_off;
+    rows_valid = si.q_len - q_tile_start;
+  }
 #ifdef SAGE_TRACE
   const bool trace_on = blockIdx.x == 0 && row == 0;
 #endif
@@ -323,12 +404,28 @@ __device__ __forceinline__ void softmax_epilogue(const AttnKernelParams& p, int 
     case 6: epilogue_convert<D, true, true, false>(oall, inv_d, vs_addr, vmp, orow, ox); break;
     default: epilogue_convert<D, true, true, true>(oall, inv_d, vs_addr, vmp, orow, ox); break;
   }
+  if constexpr (kVarlen) {
+    if (rows_valid < kTileQ) {
+      // last tile of a sequence: a bulk tensor store would run into the next sequence's rows, so every thread
+      // copies its own row (which it has just written to the staging tile) to global memory
+      if (row < rows_valid) {
+        uint8_t* dst = reinterpret_cast<uint8_t*>(p.o) +
+                       ((long long)(q_off + q_row) * p.o_stride_n + (long long)h * p.o_stride_h) * 2;
+#pragma unroll
+        for (int c0 = 0; c0 < D; c0 += 8) {
+          const uint32_t chunk = (uint32_t)((c0 & 63) >> 3);
+          const int4 v = ld_shared_v4(orow + (uint32_t)(c0 >> 6) * (kTileQ * 128) + ((chunk ^ ox) << 4));
+          *reinterpret_cast<int4*>(dst + c0 * 2) = v;
+        }
+      }
+    }
+  }
   fence_proxy_async_smem();
   named_bar_sync(3 + t, kTileQ);
-  if (row == 0) {
+  if (row == 0 && (!kVarlen || rows_valid >= kTileQ)) {
 #pragma unroll
     for (int c = 0; c < D / 64; ++c)
-      tma_store_4d(tmO, o_smem + c * (kTileQ * 128), c * 64, q_tile_start, h, b);
+      tma_store_4d(tmO, o_smem + c * (kTileQ * 128), c * 64, q_off + q_tile_start, h, kVarlen ? 0 : b);
     tma_store_commit();
   }
   const bool store = q_row < p.Nq;
@@ -474,6 +571,13 @@ static int check_attn_args(const sage_attn_args* a) {
   SAGE_REQUIRE(a->o.stride_n % 8 == 0 && a->o.stride_h % 8 == 0 && a->o.stride_b % 8 == 0 &&
                (reinterpret_cast<uintptr_t>(a->o.ptr) & 15) == 0, "output rows must be 16-byte aligned");
   SAGE_REQUIRE(a->B <= 65535 && a->Hq <= 65535, "batch / heads exceed grid limits");
+  if (a->cu_seqlens_q != nullptr) {
+    SAGE_REQUIRE(a->cu_seqlens_k && a->cu_seqlens_q_scale && a->cu_seqlens_k_scale && a->cu_pairs && a->nseq > 0,
+                 "varlen: all five prefix arrays and nseq are needed");
+    SAGE_REQUIRE(a->B == 1 && a->gran == SAGE_GRAN_PER_BLOCK, "varlen: packed tensors are passed as B = 1 with per-block scales");
+    SAGE_REQUIRE(a->mask == nullptr && a->lse == nullptr && a->v_scale == nullptr && a->v_mean == nullptr && a->d_og == 0,
+                 "varlen: attn_mask, LSE, fp8 V, v_mean and head_dim folding are not supported");
+  }
   if (a->mask != nullptr) {
     SAGE_REQUIRE(a->mask_kind >= 1 && a->mask_kind <= 3, "attn_mask kind must be 1 (bool), 2 (f16) or 3 (bf16), got %d", a->mask_kind);
     SAGE_REQUIRE(!a->is_causal, "attn_mask must be null for causal attention");

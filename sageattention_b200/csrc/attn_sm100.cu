@@ -96,7 +96,7 @@ struct SmemLayout {
 };
 
 // The kv steps of one work item for Q tile `t` (128 threads, thread = query row).
-template <int D, bool kFp8, bool kMask>
+template <int D, bool kFp8, bool kMask, bool kVarlen = false>
 __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, int row,
                                               const ItemCtx& c, const WorkItem* ring, uint32_t it,
                                               uint32_t tmem_base, uint8_t* p_smem, uint64_t* s_full,
@@ -157,8 +157,13 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
       const int blk64 = j * 2 + (k >> 2);
       if (p.gran == 3) idx = blk64 * 4 + (k & 3);
       else idx = blk64;  // per_warp / per_block: one scale per 64 kv rows
-      idx = min(idx, p.k_scale_per_bh - 1);
-      sc[k] = __ldg(ksp + idx) * qs;
+      if constexpr (kVarlen) {
+        idx = max(min(idx, c.ks_count - 1), 0);   // (0 blocks: the key-less sequence's one masked step)
+        sc[k] = __ldg(ksp + (size_t)idx * c.ks_stride) * qs;
+      } else {
+        idx = min(idx, p.k_scale_per_bh - 1);
+        sc[k] = __ldg(ksp + idx) * qs;
+      }
     }
     // pull the next steps' k scales towards L1 (a 128-byte line holds 4 (per_thread) / 16 steps)
     if (SAGE_KPREF) prefetch_l1(ksp + min((j + 2) * (p.gran == 3 ? 8 : 2), p.k_scale_per_bh - 1));
@@ -183,9 +188,10 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
       for (int c = 0; c < 128; ++c) dst[c] = (int)s[c];
     }
     const int kv0 = j * kTileKV;
-    int lim = p.Nk - 1 - kv0;
+    const int k_len = kVarlen ? c.k_len : p.Nk;
+    int lim = k_len - 1 - kv0;
     if (p.causal) lim = min(lim, q_row - kv0);
-    const bool masked_tile = (j == n_iter - 1) && (p.causal || (p.Nk - kv0) < kTileKV);
+    const bool masked_tile = (j == n_iter - 1) && (p.causal || (k_len - kv0) < kTileKV);
     float alpha, bias[8], dsum;
     if constexpr (kMask) {
       // attn_mask: max, exponentials and row sum of y = logit + mask in one call (softmax_sm100.cuh)
@@ -332,7 +338,7 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
 }
 
 // ------------------------------------------------------------------------------------------
-template <int D, bool kFp8, bool kMask = false>
+template <int D, bool kFp8, bool kMask = false, bool kVarlen = false>
 __global__ void __launch_bounds__(kThreads, 1)
 sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                      const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmO,
@@ -404,18 +410,19 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     const int row = threadIdx.x & 127;
     WgState st{0u, 0u, false};
     uint32_t it = 0;
-    ItemCtx c = softmax_setup<D>(p, t, row, ring, sched_full, it);
+    ItemCtx c = softmax_setup<D, kVarlen>(p, t, row, ring, sched_full, it);
     while (c.valid) {
       float m_run = 0.f, d_run = 1.f;
       if (c.n_iter > 0)
-        softmax_steps<D, kFp8, kMask>(p, t, row, c, ring, it, tmem_base, smem + L::kPOff + t * L::kPBytes,
+        softmax_steps<D, kFp8, kMask, kVarlen>(p, t, row, c, ring, it, tmem_base, smem + L::kPOff + t * L::kPBytes,
                                s_full, s_free, p_full, p_empty, st, m_run, d_run);
       // the next item is prepared under this item's last P.V
       const bool had_steps = c.n_iter > 0;
-      c = softmax_setup<D>(p, t, row, ring, sched_full, it + 1);
-      if (had_steps)
-        softmax_epilogue<D, kFp8>(p, t, row, ring, it, tmem_base, smem + L::kOOff + t * L::kOBytes,
+      c = softmax_setup<D, kVarlen>(p, t, row, ring, sched_full, it + 1);
+      if (had_steps) {
+        softmax_epilogue<D, kFp8, kVarlen>(p, t, row, ring, it, tmem_base, smem + L::kOOff + t * L::kOBytes,
                                   reinterpret_cast<float*>(smem + L::kVsOff) + (it % kSchedSlots) * 128, &tmO, o_full, st, m_run, d_run);
+      }
       mbar_arrive(&sched_empty[it % kSchedSlots]);
       ++it;
     }
@@ -438,44 +445,47 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
           mbar_arrive(&sched_full[slot]);
         }
       };
-      WorkItem cur = decode_work(p, blockIdx.x);
+      WorkItem cur = decode_work<kVarlen>(p, blockIdx.x);
       publish(0, cur);
       while (cur.q_pair >= 0) {
         // ticket of the NEXT item: issued now, consumed after this item's first loads are on their way
         const unsigned int ticket = atomicAdd(p.sched_counter, 1u);
         int n_it[2];
-        item_iters(p, cur.q_pair, n_it);
+        item_iters_of<kVarlen>(p, cur, n_it);
         const int n_max = max(n_it[0], n_it[1]);
         const int hkv = cur.hkv;
-        const int q_start = cur.q_pair * 2 * kTileQ;
+        // kVarlen: rows are tokens of the pack (sequence offset added), the batch coordinate is 0
+        const SeqInfo si = seq_info<kVarlen>(p, cur.b);
+        const int cb = kVarlen ? 0 : cur.b;
+        const int q_start = si.q_off + cur.q_pair * 2 * kTileQ;
         const uint32_t qb = ip % kQStages;
         mbar_wait(&q_empty[qb], ((ip / kQStages) & 1u) ^ 1u);
         mbar_arrive_expect_tx(&q_full[qb], 2 * L::kQBytes);
         uint8_t* qdst = smem + L::kQOff + qb * 2 * L::kQBytes;
-        tma_load_4d(qdst, &tmQ, &q_full[qb], 0, q_start, cur.h, cur.b);
-        tma_load_4d(qdst + L::kQBytes, &tmQ, &q_full[qb], 0, q_start + kTileQ, cur.h, cur.b);
+        tma_load_4d(qdst, &tmQ, &q_full[qb], 0, q_start, cur.h, cb);
+        tma_load_4d(qdst + L::kQBytes, &tmQ, &q_full[qb], 0, q_start + kTileQ, cur.h, cb);
         WorkItem nxt;
         for (int j = 0; j < n_max; ++j) {
           const uint32_t ks = kc % kKStages, vs = vc % kVStages;
           mbar_wait(&k_empty[ks], ((kc / kKStages) & 1u) ^ 1u);
           mbar_arrive_expect_tx(&k_full[ks], L::kKBytes);
-          tma_load_4d(smem + L::kKOff + ks * L::kKBytes, &tmK, &k_full[ks], 0, j * kTileKV, hkv, cur.b);
+          tma_load_4d(smem + L::kKOff + ks * L::kKBytes, &tmK, &k_full[ks], 0, si.k_off + j * kTileKV, hkv, cb);
           mbar_wait(&v_empty[vs], ((vc / kVStages) & 1u) ^ 1u);
           mbar_arrive_expect_tx(&v_full[vs], L::kVBytes);
           uint8_t* vdst = smem + L::kVOff + vs * L::kVBytes;
           if constexpr (kFp8) {
             // V^T e4m3 [D rows][128 kv] (kv contiguous)
-            tma_load_4d(vdst, &tmV, &v_full[vs], j * kTileKV, 0, hkv, cur.b);
+            tma_load_4d(vdst, &tmV, &v_full[vs], j * kTileKV, 0, hkv, cb);
           } else {
             // V f16 [128 kv][D]: one 64-wide (128 B) column block per load
 #pragma unroll
             for (int c = 0; c < D / 64; ++c)
-              tma_load_4d(vdst + c * (kTileKV * 128), &tmV, &v_full[vs], c * 64, j * kTileKV, hkv, cur.b);
+              tma_load_4d(vdst + c * (kTileKV * 128), &tmV, &v_full[vs], c * 64, si.k_off + j * kTileKV, hkv, cb);
           }
           ++kc;
           ++vc;
           if (j == 0) {
-            nxt = decode_work(p, gridDim.x + ticket);
+            nxt = decode_work<kVarlen>(p, gridDim.x + ticket);
             publish(ip + 1, nxt);
           }
         }
@@ -577,7 +587,7 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         mbar_arrive(&sched_empty[0]);
         have = w0.q_pair >= 0;
         if (have) {
-          item_iters(p, w0.q_pair, n_it);
+          item_iters_of<kVarlen>(p, w0, n_it);
           mbar_wait(&q_full[0], 0);
           qk_step(n_it, 0, 0);
         }
@@ -586,7 +596,7 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         const WorkItem wn = read_work(ring, sched_full, im + 1);
         mbar_arrive(&sched_empty[(im + 1) % kSchedSlots]);
         const bool have_nxt = wn.q_pair >= 0;
-        if (have_nxt) item_iters(p, wn.q_pair, n_nx);
+        if (have_nxt) item_iters_of<kVarlen>(p, wn, n_nx);
         const int n_max = max(n_it[0], n_it[1]);
         const uint32_t qb = im % kQStages;
         for (int j = 0; j < n_max; ++j) {
@@ -635,7 +645,7 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
 // ==========================================================================================
 namespace sage {
 
-template <int D, bool kFp8, bool kMask = false>
+template <int D, bool kFp8, bool kMask = false, bool kVarlen = false>
 static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
   using L = SmemLayout<D, kFp8>;
   CUtensorMap tmQ, tmK, tmV, tmO;
@@ -699,7 +709,10 @@ static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
   p.mask = reinterpret_cast<const uint8_t*>(a->mask);
   p.mask_kind = a->mask_kind;
   p.mask_sb = a->mask_stride_b; p.mask_sh = a->mask_stride_h; p.mask_sm = a->mask_stride_m;
-  auto kern = sage_attn_fwd_kernel<D, kFp8, kMask>;
+  SAGE_REQUIRE(kVarlen == (a->cu_seqlens_q != nullptr), "internal: varlen kernel selection");
+  p.cu_q = a->cu_seqlens_q; p.cu_k = a->cu_seqlens_k; p.cu_q_scale = a->cu_seqlens_q_scale;
+  p.cu_k_scale = a->cu_seqlens_k_scale; p.cu_pairs = a->cu_pairs; p.nseq = a->nseq;
+  auto kern = sage_attn_fwd_kernel<D, kFp8, kMask, kVarlen>;
   // per template instantiation AND per device: function attributes belong to the device's context
   static SmemAttrOnce smem_attr;
   SAGE_CUDA(smem_attr.ensure(kern, L::kDynamic));
@@ -712,7 +725,8 @@ static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
   SAGE_CUDA(cudaMemsetAsync(p.sched_counter, 0, sizeof(unsigned int), stream));
   int ctas = sm_count();
   if (a->max_ctas > 0 && a->max_ctas < ctas) ctas = a->max_ctas;
-  const int grid = (int)(n_work < ctas ? n_work : ctas);
+  // kVarlen: the number of items is only known on the device (cu_pairs): one CTA per SM, the surplus ones leave at once
+  const int grid = kVarlen ? ctas : (int)(n_work < ctas ? n_work : ctas);
   kern<<<grid, kThreads, L::kDynamic, stream>>>(tmQ, tmK, tmV, tmO, p);
   SAGE_CUDA(cudaGetLastError());
   return 0;
@@ -724,6 +738,7 @@ static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
 // S(j) is drained); called from sage_attn_i8_f16 in attn_f16_sm100.cu
 namespace sage {
 int launch_attn_f16_d64(const sage_attn_args* a, cudaStream_t stream) {
+  if (a->cu_seqlens_q != nullptr) return launch_attn<64, false, false, true>(a, stream);
   return a->mask ? launch_attn<64, false, true>(a, stream) : launch_attn<64, false>(a, stream);
 }
 }  // namespace sage
@@ -737,6 +752,7 @@ extern "C" int sage_debug_trace(long long* out) {
 extern "C" int sage_attn_i8_f8(const sage_attn_args* a, void* stream) {
   int rc = sage::check_attn_args(a);
   if (rc) return rc;
+  SAGE_REQUIRE(a->cu_seqlens_q == nullptr, "varlen is an f16-P.V path (sage_attn_i8_f16)");
   cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
   if (a->mask != nullptr)
     return a->D == 128 ? sage::launch_attn<128, true, true>(a, s) : sage::launch_attn<64, true, true>(a, s);

@@ -336,3 +336,55 @@ def per_channel_fp8(v, tensor_layout="HND", scale_max=448.0, smooth_v=True, _n_s
                                             _dtype_code(v), float(scale_max), 1 if smooth_v else 0,
                                             ws.data_ptr(), _stream(v)))
     return v_fp8, v_scale, vm
+
+
+def per_block_int8_varlen(q, k, cu_seqlens_q, cu_seqlens_k, max_seqlen_q, max_seqlen_k, BLKQ=128, BLKK=64, sm_scale=None,
+                          km=None):
+    """Per-block INT8 quantisation of a packed variable-length batch in ONE launch, bit for bit the reference's
+    Triton `per_block_int8` (/root/reference/sageattention/triton/quant_per_block_varlen.py:59-107): q [Tq, Hq, D] is
+    pre-scaled by sm_scale * 1.44269504, blocks of BLKQ / BLKK rows restart at every sequence, scale = amax / 127 with
+    no floor, round half away from zero.  `km` ([Hkv, D] or broadcastable, k's dtype): subtracted from k first, like
+    the `k - km` of core.py:462-463, inside the same launch.
+
+    Returns (q_int8, q_scale, k_int8, k_scale, cu_seqlens_q_scale, cu_seqlens_k_scale) as the reference does, with
+    one difference that keeps the call free of host synchronisation: the scale arrays have ceil(T / BLK) + batch rows
+    (an upper bound); rows [0, cu_seqlens_*_scale[-1]) are the reference's, the rest is never written.  The work-list
+    prefix the attention kernel needs is returned as a 7th element."""
+    _require_cuda(q, k)
+    if BLKQ != 128 or BLKK != 64:
+        raise ValueError("the sm_100a kernels use BLKQ = 128 and BLKK = 64")
+    if q.dim() != 3 or k.dim() != 3:
+        raise ValueError("q and k must be [tokens, heads, head_dim]")
+    lib = _lib.load()
+    tq, hq, d = q.shape
+    tk, hk, _ = k.shape
+    if d not in (64, 128):
+        raise ValueError("head_dim must be 64 or 128 (pad first)")
+    if q.stride(-1) != 1 or k.stride(-1) != 1:
+        raise ValueError("last dim of q / k must be contiguous")
+    if sm_scale is None:
+        sm_scale = d ** -0.5
+    nseq = cu_seqlens_q.numel() - 1
+    cu_q = cu_seqlens_q.to(torch.int32).contiguous()
+    cu_k = cu_seqlens_k.to(torch.int32).contiguous()
+    dev = q.device
+    q_int8 = torch.empty((tq, hq, d), dtype=torch.int8, device=dev)
+    k_int8 = torch.empty((tk, hk, d), dtype=torch.int8, device=dev)
+    q_scale = torch.empty(((tq + 127) // 128 + nseq, hq), dtype=torch.float32, device=dev)
+    k_scale = torch.empty(((tk + 63) // 64 + nseq, hk), dtype=torch.float32, device=dev)
+    cu_qs = torch.empty(nseq + 1, dtype=torch.int32, device=dev)
+    cu_ks = torch.empty(nseq + 1, dtype=torch.int32, device=dev)
+    cu_pairs = torch.empty(nseq + 1, dtype=torch.int32, device=dev)
+    km_ptr = None
+    if km is not None:
+        km = km.reshape(hk, d).contiguous()
+        if km.dtype != k.dtype:
+            raise RuntimeError("km must have the same dtype as k")
+        km_ptr = km.data_ptr()
+    with _on_device(dev):
+        _lib.check(lib.sage_quant_per_block_varlen_int8(
+            q.data_ptr(), k.data_ptr(), km_ptr, q_int8.data_ptr(), k_int8.data_ptr(), q_scale.data_ptr(),
+            k_scale.data_ptr(), cu_q.data_ptr(), cu_k.data_ptr(), cu_qs.data_ptr(), cu_ks.data_ptr(), cu_pairs.data_ptr(),
+            nseq, hq, hk, d, _dtype_code(q), int(max_seqlen_q), int(max_seqlen_k), q.stride(0), q.stride(1), k.stride(0),
+            k.stride(1), float(sm_scale) * 1.44269504, _stream(q)))
+    return q_int8, q_scale, k_int8, k_scale, cu_qs, cu_ks, (cu_q, cu_k, cu_pairs)
