@@ -76,13 +76,25 @@ def main():
 
     import sageattention_b200 as sb
     from sageattention_b200 import core
+    import time
+    import bench
     dev = "cuda:0"
+    # every line carries the SM clocks / throttle reasons sampled while it was measured (numbers without a clock
+    # record are not evidence)
+    sampler = bench.ClockSampler(0)
+    sampler.start()
+    sampler.wait_first()
     B, H = args.batch, args.heads
     gran = 3 if args.gran == "per_thread" else 2
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
     out = open(args.out, "a")
 
+    t_mark = [time.monotonic()]
+
     def emit(rec):
+        now = time.monotonic()
+        rec["clocks"] = sampler.window(t_mark[0], now)
+        t_mark[0] = now
         line = json.dumps(rec)
         print(line, flush=True)
         out.write(line + "\n")
