@@ -205,6 +205,40 @@ typedef struct sage_attn_args {
 int sage_attn_i8_f16(const sage_attn_args* a, void* stream);
 int sage_attn_i8_f8(const sage_attn_args* a, void* stream);
 
+/* The whole operator behind ONE call and ONE workspace: quantisation prologue (smooth_k on, smooth_v off) + attention,
+ * for the default paths of sageattn / sageattn_qk_int8_pv_fp8_cuda (/root/reference/sageattention/core.py:656-905) and
+ * sageattn_qk_int8_pv_fp16_cuda (core.py:480-653).  It launches exactly what sage_prepass_qkv_fp8 /
+ * sage_prepass_qk_int8[_v16] followed by sage_attn_i8_f8 / sage_attn_i8_f16 launch (results bit-identical); what it
+ * saves is host time: the caller makes two allocations (workspace, o) and one foreign call instead of 6-8 and 2-3.
+ * q, k, v, o: the caller's tensors ([B,H,N,d_og] or [B,N,H,d_og], any strides with contiguous rows).  workspace:
+ * sage_sageattn_fwd_workspace_bytes() bytes, 256-byte aligned, contents undefined afterwards.  km_out: NULL, or
+ * [B,Hkv,D] in the input dtype to receive mean(K) (the LSE correction needs it, core.py:613-617).  lse: NULL or f32
+ * [B,Hq,Nq] (base 2, uncorrected).  ev_start / ev_stop: NULL, or cudaEvent_t recorded on the stream around the attention
+ * launch alone (bench.py's kernel-only figure). */
+typedef struct {
+  sage_tensor4 q, k, v, o;
+  void* workspace;
+  size_t workspace_bytes;
+  void* km_out;
+  float* lse;
+  void* ev_start;
+  void* ev_stop;
+  int B, Hq, Hkv, Nq, Nk;
+  int D;          /* 64 or 128: head_dim after padding */
+  int d_og;       /* 0 = D, else the real head_dim (multiple of 8) */
+  int dtype;      /* SAGE_DTYPE_* of q, k, v, o */
+  int layout_hnd; /* 1: [B,H,N,D], 0: [B,N,H,D] (the reference's _tensor_layout) */
+  int pv_fp8;     /* 1: e4m3 P.V (sageattn), 0: f16 P.V */
+  int per_thread; /* 1: per_thread, 0: per_warp */
+  int warp_q;     /* 32, or 16 */
+  int is_causal;
+  int max_ctas;   /* 0 = one CTA per SM */
+  float sm_scale;
+  float v_scale_max; /* fp8 P.V: 448 or 2.25 (core.py:818-820) */
+} sage_fwd_args;
+size_t sage_sageattn_fwd_workspace_bytes(const sage_fwd_args* a);
+int sage_sageattn_fwd(const sage_fwd_args* a, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -35,6 +35,17 @@ class AttnArgs(ctypes.Structure):
     ]
 
 
+class FwdArgs(ctypes.Structure):
+    _fields_ = [
+        ("q", Tensor4), ("k", Tensor4), ("v", Tensor4), ("o", Tensor4),
+        ("workspace", c_vp), ("workspace_bytes", ctypes.c_size_t), ("km_out", c_vp), ("lse", c_vp),
+        ("ev_start", c_vp), ("ev_stop", c_vp),
+        ("B", c_int), ("Hq", c_int), ("Hkv", c_int), ("Nq", c_int), ("Nk", c_int), ("D", c_int), ("d_og", c_int),
+        ("dtype", c_int), ("layout_hnd", c_int), ("pv_fp8", c_int), ("per_thread", c_int), ("warp_q", c_int),
+        ("is_causal", c_int), ("max_ctas", c_int), ("sm_scale", c_f32), ("v_scale_max", c_f32),
+    ]
+
+
 # name -> (restype, argtypes); the single source of truth for the exported surface
 SIGNATURES = {
     "sage_last_error": (ctypes.c_char_p, []),
@@ -60,6 +71,8 @@ SIGNATURES = {
                                      c_int, c_int, c_int, c_f32, c_int, c_vp, c_vp]),
     "sage_attn_i8_f16": (c_int, [ctypes.POINTER(AttnArgs), c_vp]),
     "sage_attn_i8_f8": (c_int, [ctypes.POINTER(AttnArgs), c_vp]),
+    "sage_sageattn_fwd_workspace_bytes": (ctypes.c_size_t, [ctypes.POINTER(FwdArgs)]),
+    "sage_sageattn_fwd": (c_int, [ctypes.POINTER(FwdArgs), c_vp]),
 }
 
 _lib = None
@@ -72,6 +85,7 @@ KERNELS_PER_CALL = {
     # smooth_v: statistics + conversion; otherwise one cluster launch
     "sage_per_channel_fp8": (lambda a: 2 if a[14] else 1),
     "sage_attn_i8_f16": 1, "sage_attn_i8_f8": 1,
+    "sage_sageattn_fwd": 2,   # prologue + attention
 }
 LAUNCHES = 0
 

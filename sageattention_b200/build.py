@@ -25,6 +25,7 @@ UNITS = [
     ("prepass.cu", ["--use_fast_math"]),
     ("attn_sm100.cu", []),
     ("attn_f16_sm100.cu", []),
+    ("fwd.cu", []),
 ]
 
 

@@ -183,6 +183,77 @@ def _launch(fp8, q_int8, k_int8, v, o, q_scale, k_scale, v_scale, v_mean, tensor
     return lse
 
 
+# One foreign call + one workspace per operator call (sage_sageattn_fwd) on the default paths; False = the two-call
+# path with one tensor per intermediate (kept for the non-default options and as the reference the fast path is
+# tested against: results are bit-identical).
+FUSED_CALL = True
+_WS_BYTES = {}
+
+
+def _fused_forward(q, k, v, tensor_layout, is_causal, qk_quant_gran, warp_q, sm_scale, pv_fp8, v_scale_max, return_lse):
+    """sage_sageattn_fwd: prologue (smooth_k, no smooth_v) + attention from ONE ctypes crossing; the host side is two
+    allocations (workspace, output; two more with return_lse).  Host time per call about 25 us against about 75 us for
+    the two-call path (tools/host_overhead.py)."""
+    lib = _lib.load()
+    hnd = tensor_layout == "HND"
+    if hnd:
+        b, hq, nq, d_og = q.shape
+        hk, nk = k.shape[1], k.shape[2]
+        hi, ni = 1, 2
+    elif tensor_layout == "NHD":
+        b, nq, hq, d_og = q.shape
+        nk, hk = k.shape[1], k.shape[2]
+        hi, ni = 2, 1
+    else:
+        raise ValueError(f"Unknown tensor layout: {tensor_layout}")
+    d = 64 if d_og <= 64 else 128
+    dev = q.device
+    T4 = _lib.Tensor4
+    o = torch.empty(q.shape, dtype=q.dtype, device=dev)
+    a = _lib.FwdArgs()
+    a.q = T4(q.data_ptr(), q.stride(0), q.stride(hi), q.stride(ni))
+    a.k = T4(k.data_ptr(), k.stride(0), k.stride(hi), k.stride(ni))
+    a.v = T4(v.data_ptr(), v.stride(0), v.stride(hi), v.stride(ni))
+    a.o = T4(o.data_ptr(), o.stride(0), o.stride(hi), o.stride(ni))
+    a.B, a.Hq, a.Hkv, a.Nq, a.Nk, a.D = b, hq, hk, nq, nk, d
+    a.d_og = d_og if d_og != d else 0
+    a.dtype = _dtype_code(q)
+    a.layout_hnd = 1 if hnd else 0
+    a.pv_fp8 = 1 if pv_fp8 else 0
+    a.per_thread = 1 if qk_quant_gran == "per_thread" else 0
+    a.warp_q = warp_q
+    a.is_causal = 1 if is_causal else 0
+    a.max_ctas = int(GRID_LIMIT) if GRID_LIMIT else 0
+    a.sm_scale = float(sm_scale)
+    a.v_scale_max = float(v_scale_max)
+    key = (b, hq, hk, nq, nk, d, d_og, a.dtype, a.pv_fp8, a.per_thread, warp_q)
+    nbytes = _WS_BYTES.get(key)
+    if nbytes is None:
+        nbytes = lib.sage_sageattn_fwd_workspace_bytes(a)
+        if nbytes == 0:
+            _lib.check(-1)
+        _WS_BYTES[key] = nbytes
+    ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+    a.workspace, a.workspace_bytes = ws.data_ptr(), nbytes
+    lse = km = None
+    if return_lse:
+        lse = torch.empty((b, hq, nq), dtype=torch.float32, device=dev)
+        km = torch.empty((b, hk, d), dtype=k.dtype, device=dev)
+        a.lse, a.km_out = lse.data_ptr(), km.data_ptr()
+    ev = None
+    if KERNEL_EVENTS is not None:
+        ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+        for e in ev:
+            e.record()   # creates the underlying cudaEvent_t; the library records it again around the attention launch
+        a.ev_start, a.ev_stop = ev[0].cuda_event, ev[1].cuda_event
+    with _on_device(dev):
+        _lib.check(lib.sage_sageattn_fwd(a, _stream(q)))
+    if ev is not None:
+        KERNEL_EVENTS.append(ev)
+    corr = _lse_correction(q, km[..., :d_og], tensor_layout) if return_lse else None
+    return _finish(o, lse, corr, sm_scale, d_og, return_lse)
+
+
 def _finish(o, lse, lse_correction, sm_scale, head_dim_og, return_lse):
     o = o[..., :head_dim_og]
     if not return_lse:
@@ -231,6 +302,9 @@ def sageattn_qk_int8_pv_fp16_cuda(
     if sm_scale is None:
         sm_scale = head_dim_og ** -0.5
     warp_q = 16 if (head_dim_og > 64 and pv_accum_dtype == "fp16+fp32") else 32
+    if FUSED_CALL and smooth_k and not smooth_v and q.dim() == 4 and v.shape == k.shape and \
+            (fold or head_dim_og in (64, 128)):
+        return _fused_forward(q, k, v, tensor_layout, is_causal, qk_quant_gran, warp_q, sm_scale, False, 0.0, return_lse)
     # a bf16 V needs an f16 copy (core.py:633): on the default path it comes out of the prologue launch
     fuse_v = smooth_k and not smooth_v and v.dtype == torch.bfloat16 and v.shape == k.shape
     qk = _quantize_qk(q, k, smooth_k, qk_quant_gran, tensor_layout, warp_q, return_lse, fold,
@@ -289,8 +363,12 @@ def sageattn_qk_int8_pv_fp8_cuda(
     assert q.stride(-1) == 1 and k.stride(-1) == 1 and v.stride(-1) == 1, "Last dim of qkv must be contiguous."
     if sm_scale is None:
         sm_scale = head_dim_og ** -0.5
-    o = torch.empty(q.size(), dtype=dtype, device=q.device)
     quant_v_scale_max = 2.25 if pv_accum_dtype == "fp32+fp16" else 448.0
+    if FUSED_CALL and smooth_k and not smooth_v and q.dim() == 4 and k.shape == v.shape and \
+            (fold or head_dim_og in (64, 128)):
+        return _fused_forward(q, k, v, tensor_layout, is_causal, qk_quant_gran, 32, sm_scale, True, quant_v_scale_max,
+                              return_lse)
+    o = torch.empty(q.size(), dtype=dtype, device=q.device)
     kv_len = k.size(2) if tensor_layout == "HND" else k.size(1)
     # the reference zero-pads V to a multiple of 128 tokens first (core.py:822-828); the kernels
     # reproduce that padding's effect on Npad / the smooth_v mean without the extra copy

@@ -63,6 +63,12 @@ namespace sage {
 #ifndef SAGE_MAXTREE
 #define SAGE_MAXTREE 0
 #endif
+// 1: the k scales of a kv step as two 16-byte loads (per_thread) / two scalars (per_warp) instead of eight indexed loads.
+// Measured (one box, kernel-only, N = 8K / 32K): +3 % in the f16 hd128 kernel (attn_f16_sm100.cu: 1253 -> 1299 / 1161 ->
+// 1198 TOPS, where it is on) but -2 % (fp8 hd128: 1304 -> 1283) and -5 % (fp8 hd64: 679 -> 648) here, so off.
+#ifndef SAGE_KSVEC
+#define SAGE_KSVEC 0
+#endif
 // 0: exp, pack and store are separate phases.  1: the e4m3 / f16 conversions are issued group by group (16
 // columns) inside the exp phase, under the MUFU pipe.  2: as 1, and every group is stored (shared memory or
 // TMEM) as soon as it is packed, so that only the fence and the barrier arrival are left after the window.
@@ -151,18 +157,38 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
     const uint32_t ph = st.steps & 1u;
     // k scales of this tile -> 8 class scales
     float sc[8];
+    if constexpr (!kVarlen) {
+      if (SAGE_KSVEC && p.gran == 3) {
+        // per_thread: the 8 scales of kv tile j are 8 consecutive floats (2 blocks of 64 rows x 4 groups): two 16-byte
+        // loads instead of eight indexed ones.  A second block beyond kv_len (ragged last tile) has no scales: all its
+        // columns are masked, any finite factor will do - the first block's are reused
+        const float4 s0 = __ldg(reinterpret_cast<const float4*>(ksp + j * 8));
+        const float4 s1 = (j * 8 + 4 < p.k_scale_per_bh) ? __ldg(reinterpret_cast<const float4*>(ksp + j * 8 + 4)) : s0;
+        sc[0] = s0.x * qs; sc[1] = s0.y * qs; sc[2] = s0.z * qs; sc[3] = s0.w * qs;
+        sc[4] = s1.x * qs; sc[5] = s1.y * qs; sc[6] = s1.z * qs; sc[7] = s1.w * qs;
+      } else if (SAGE_KSVEC && p.gran != 3) {
+        // per_warp / per_block: one scale per 64 kv rows
+        const float a0 = __ldg(ksp + min(j * 2, p.k_scale_per_bh - 1)) * qs;
+        const float a1 = __ldg(ksp + min(j * 2 + 1, p.k_scale_per_bh - 1)) * qs;
+        sc[0] = sc[1] = sc[2] = sc[3] = a0;
+        sc[4] = sc[5] = sc[6] = sc[7] = a1;
+      } else {
 #pragma unroll
-    for (int k = 0; k < 8; ++k) {
-      int idx;
-      const int blk64 = j * 2 + (k >> 2);
-      if (p.gran == 3) idx = blk64 * 4 + (k & 3);
-      else idx = blk64;  // per_warp / per_block: one scale per 64 kv rows
-      if constexpr (kVarlen) {
+        for (int k = 0; k < 8; ++k) {
+          int idx;
+          const int blk64 = j * 2 + (k >> 2);
+          if (p.gran == 3) idx = blk64 * 4 + (k & 3);
+          else idx = blk64;  // per_warp / per_block: one scale per 64 kv rows
+          idx = min(idx, p.k_scale_per_bh - 1);
+          sc[k] = __ldg(ksp + idx) * qs;
+        }
+      }
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        int idx = j * 2 + (k >> 2);             // per-block scales of the sequence, [blocks, H]
         idx = max(min(idx, c.ks_count - 1), 0);   // (0 blocks: the key-less sequence's one masked step)
         sc[k] = __ldg(ksp + (size_t)idx * c.ks_stride) * qs;
-      } else {
-        idx = min(idx, p.k_scale_per_bh - 1);
-        sc[k] = __ldg(ksp + idx) * qs;
       }
     }
     // pull the next steps' k scales towards L1 (a 128-byte line holds 4 (per_thread) / 16 steps)

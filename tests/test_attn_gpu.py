@@ -388,3 +388,36 @@ def test_graph_replay_overlapping_eager_launches_on_another_stream(pv):
         torch.cuda.synchronize()
         bad += int(not torch.equal(oa, oa_ref)) + int(not torch.equal(ob, ob_ref))
     assert bad == 0
+
+
+@pytest.mark.parametrize("fn,kw", [
+    ("sageattn", {}),
+    ("sageattn_qk_int8_pv_fp8_cuda", {"pv_accum_dtype": "fp32+fp16"}),
+    ("sageattn_qk_int8_pv_fp8_cuda", {"qk_quant_gran": "per_warp", "pv_accum_dtype": "fp32+fp32"}),
+    ("sageattn_qk_int8_pv_fp16_cuda", {}),
+    ("sageattn_qk_int8_pv_fp16_cuda", {"pv_accum_dtype": "fp16+fp32", "qk_quant_gran": "per_warp"}),
+])
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("layout", ["HND", "NHD"])
+@pytest.mark.parametrize("shape", [(2, 4, 2, 512, 512, 128, False), (1, 4, 4, 300, 777, 64, False), (1, 2, 2, 200, 200, 96, True),
+                                   (1, 6, 2, 1000, 1000, 128, True)])
+def test_single_call_operator_equals_two_call_path(fn, kw, dtype, layout, shape):
+    """sage_sageattn_fwd (one foreign call, one workspace: the default path of the operators) launches what the
+    separate prologue and attention entry points launch: output and LSE must be BIT-identical to the two-call path
+    (GQA, ragged and cross lengths, folded head_dim, both layouts and dtypes, per_warp with WARPQ 16 / 32)."""
+    b, hq, hk, nq, nk, d, causal = shape
+    q, k, v = make_qkv(b, hq, hk, nq, nk, d, dtype, seed=23)
+    if layout == "NHD":
+        q, k, v = (t.transpose(1, 2).contiguous() for t in (q, k, v))
+    f = getattr(sb, fn)
+    assert core.FUSED_CALL
+    o1, l1 = f(q, k, v, tensor_layout=layout, is_causal=causal, return_lse=True, **kw)
+    o1b = f(q, k, v, tensor_layout=layout, is_causal=causal, **kw)
+    core.FUSED_CALL = False
+    try:
+        o2, l2 = f(q, k, v, tensor_layout=layout, is_causal=causal, return_lse=True, **kw)
+    finally:
+        core.FUSED_CALL = True
+    torch.cuda.synchronize()
+    assert o1.shape == q.shape and o1.is_contiguous()
+    assert torch.equal(o1, o2) and torch.equal(o1b, o2) and torch.equal(l1, l2)

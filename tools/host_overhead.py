@@ -6,7 +6,8 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import sageattention_b200 as S
 
 q, k, v = (torch.randn(4, 32, 4096, 128, device="cuda", dtype=torch.float16) for _ in range(3))
-fn = S.sageattn_qk_int8_pv_fp16_cuda
+fn = getattr(S, sys.argv[1]) if len(sys.argv) > 1 else S.sageattn_qk_int8_pv_fp16_cuda
+print("entry point:", fn.__name__)
 for _ in range(5):
     fn(q, k, v)
 torch.cuda.synchronize()
@@ -28,4 +29,4 @@ for _ in range(n):
     fn(qs, ks, vs)
 pr.disable()
 torch.cuda.synchronize()
-pstats.Stats(pr).sort_stats("cumulative").print_stats(18)
+pstats.Stats(pr).sort_stats("cumulative").print_stats(int(sys.argv[2]) if len(sys.argv) > 2 else 18)
