@@ -10,13 +10,14 @@ sys.path.insert(0, ROOT)
 from sageattention_b200 import build as B  # noqa: E402
 
 
-def build_variant(name, flags):
+def build_variant(name, flags, only=None):
+    """`only`: apply the flags to this attention unit alone (e.g. -DSAGE_TRACE, whose dump symbol both units define)."""
     B.build()
     out = os.path.join(ROOT, "tools", "_bin")
     os.makedirs(out, exist_ok=True)
     objs, procs = [], []
     for unit, extra in B.UNITS:
-        if unit.startswith("attn_"):
+        if unit.startswith("attn_") and (only is None or unit == only):
             obj = os.path.join(out, f"{name}_{unit}.o")
             cmd = [B._nvcc(), "-c", os.path.join(B.CSRC, unit), "-o", obj] + B.ARCH + B.COMMON + extra + flags
             procs.append(subprocess.Popen(cmd))
@@ -32,4 +33,10 @@ def build_variant(name, flags):
 
 
 if __name__ == "__main__":
-    print(build_variant(sys.argv[1], sys.argv[2:]))
+    args = sys.argv[2:]
+    only = None
+    if "--only" in args:
+        i = args.index("--only")
+        only = args[i + 1]
+        del args[i:i + 2]
+    print(build_variant(sys.argv[1], args, only))
