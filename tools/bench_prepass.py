@@ -38,6 +38,8 @@ timeit("smooth_quant_k_int8(k) per_warp   [fused K]", lambda i: S.smooth_quant_k
 timeit("quant_q_int8(q) per_thread", lambda i: S.quant_q_int8(qs[i % nbuf], "per_thread"), mb * 1.5)
 timeit("prepass_qk_int8(q, k) per_thread [one launch]", lambda i: S.prepass_qk_int8(qs[i % nbuf], ks[i % nbuf], "per_thread"), 2 * mb * 1.5)
 timeit("prepass_qk_int8(q, k) per_warp   [one launch]", lambda i: S.prepass_qk_int8(qs[i % nbuf], ks[i % nbuf], "per_warp"), 2 * mb * 1.5)
+timeit("prepass_qkv_fp8(q, k, v) per_thread [one launch]",
+       lambda i: S.prepass_qkv_fp8(qs[i % nbuf], ks[i % nbuf], qs[(i + 1) % nbuf], "per_thread", _n_stat=(N + 127) // 128 * 128), 3 * mb * 1.5)
 timeit("per_channel_fp8(v, smooth_v=False) [one launch]", lambda i: S.per_channel_fp8(qs[i % nbuf], smooth_v=False), mb * 1.5)
 timeit("per_channel_fp8(v, smooth_v)", lambda i: S.per_channel_fp8(qs[i % nbuf], smooth_v=True), mb * 1.5)
 timeit("torch copy (read+write)", lambda i: qs[(i + 1) % nbuf].copy_(qs[i % nbuf]), 2 * mb)

@@ -17,7 +17,7 @@ def build_variant(name, flags, only=None):
     os.makedirs(out, exist_ok=True)
     objs, procs = [], []
     for unit, extra in B.UNITS:
-        if unit.startswith("attn_") and (only is None or unit == only):
+        if (only is None and unit.startswith("attn_")) or unit == only:
             obj = os.path.join(out, f"{name}_{unit}.o")
             cmd = [B._nvcc(), "-c", os.path.join(B.CSRC, unit), "-o", obj] + B.ARCH + B.COMMON + extra + flags
             procs.append(subprocess.Popen(cmd))
