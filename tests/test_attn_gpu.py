@@ -421,3 +421,22 @@ def test_single_call_operator_equals_two_call_path(fn, kw, dtype, layout, shape)
     torch.cuda.synchronize()
     assert o1.shape == q.shape and o1.is_contiguous()
     assert torch.equal(o1, o2) and torch.equal(o1b, o2) and torch.equal(l1, l2)
+
+
+@pytest.mark.parametrize("pv", ["f8", "f16"])
+@pytest.mark.parametrize("causal", [False, True])
+def test_capped_persistent_grid_is_bit_identical(pv, causal):
+    """sage_attn_args.max_ctas: the dynamic scheduler hands out the same work items whatever the number of CTAs, and
+    every item's arithmetic is independent of which CTA runs it - so any cap (1 CTA included) reproduces the full grid
+    bit for bit."""
+    q8, qs, k8, ks, v, vs = _random_codes(2, 8, 4, 1100, 1100, 128, pv, seed=13)
+    sm = 128 ** -0.5
+    full = run_kernel(pv, q8, qs, k8, ks, v, vs, None, 3, causal, sm, torch.float16)
+    for cap in (1, 7, 100, 100000):
+        core.GRID_LIMIT = cap
+        try:
+            o = run_kernel(pv, q8, qs, k8, ks, v, vs, None, 3, causal, sm, torch.float16)
+        finally:
+            core.GRID_LIMIT = None
+        torch.cuda.synchronize()
+        assert torch.equal(o, full), cap
