@@ -52,6 +52,8 @@ typedef struct sage_tensor4 {
 
 const char* sage_last_error(void);
 int sage_version(void);
+/* sha256 (hex) of the csrc/ and include/ sources the library was built from, "unknown" for a hand build */
+const char* sage_source_hash(void);
 
 /* km[b,h,d] = dtype( (sum_n x[b,h,n,d]) * (1/N) ); out is [B,H,D] contiguous, same dtype as x.
  * Deterministic two-level reduction; workspace of sage_seq_mean_workspace_bytes() bytes. */

@@ -50,6 +50,7 @@ class FwdArgs(ctypes.Structure):
 SIGNATURES = {
     "sage_last_error": (ctypes.c_char_p, []),
     "sage_version": (c_int, []),
+    "sage_source_hash": (ctypes.c_char_p, []),
     "sage_seq_mean_workspace_bytes": (ctypes.c_size_t, [c_int] * 4),
     "sage_seq_mean": (c_int, [Tensor4, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp]),
     "sage_seq_mean_static": (c_int, [Tensor4, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp]),
@@ -119,13 +120,44 @@ def load():
     if not os.path.exists(_LIB_PATH):
         from . import build as _build
         _build.build()
-    lib = ctypes.CDLL(_LIB_PATH)
+    try:
+        lib = _open(_LIB_PATH)
+    except AttributeError:
+        # a binary from before a symbol was added: same remedy as a hash mismatch
+        if os.environ.get("SAGE_B200_LIB"):
+            raise
+        from . import build as _build
+        _build.build(force=True)
+        lib = _open(_LIB_PATH)
+    if not os.environ.get("SAGE_B200_LIB"):
+        # a binary built from other sources than the ones next to it (edited .cu / .h, an old .so that travelled): rebuild
+        # when a compiler is at hand, else say so - never use it silently (round-1 ADVICE)
+        try:
+            from . import build as _build
+            want = _build.source_hash()
+            have = lib.sage_source_hash().decode() if hasattr(lib, "sage_source_hash") else "missing"
+            if have != want:
+                import shutil
+                import warnings
+                if shutil.which("nvcc") or os.path.exists("/usr/local/cuda/bin/nvcc"):
+                    _build.build()
+                    lib = _open(_LIB_PATH)
+                else:
+                    warnings.warn(f"libsage_b200.so was built from other sources (hash {have[:12]}, sources {want[:12]}) and "
+                                  "no nvcc is available to rebuild it")
+        except OSError:
+            pass  # sources not shipped with the package: nothing to compare with
+    _lib = _LibView(lib)
+    return _lib
+
+
+def _open(path):
+    lib = ctypes.CDLL(path)
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError if the symbol is missing: fail loudly
         fn.restype = res
         fn.argtypes = args
-    _lib = _LibView(lib)
-    return _lib
+    return lib
 
 
 def check(rc):

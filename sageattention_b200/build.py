@@ -29,6 +29,20 @@ UNITS = [
 ]
 
 
+def source_hash():
+    """sha256 over the library's sources (csrc/*.cu, *.cuh, *.h and include/sage_b200.h), in name order."""
+    import hashlib
+    h = hashlib.sha256()
+    files = sorted(f for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h")) and not f.startswith("_variant_"))
+    for f in files:
+        h.update(f.encode())
+        with open(os.path.join(CSRC, f), "rb") as fh:
+            h.update(fh.read())
+    with open(os.path.join(ROOT, "include", "sage_b200.h"), "rb") as fh:
+        h.update(fh.read())
+    return h.hexdigest()
+
+
 def _nvcc():
     return shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
 
@@ -43,12 +57,18 @@ def build(force=False, verbose=False):
     os.makedirs(OBJ, exist_ok=True)
     objs, rebuilt = [], False
     procs = []
+    digest = source_hash()
+    stamp = os.path.join(OBJ, "capi.hash")
     for name, extra in UNITS:
         src = os.path.join(CSRC, name)
         obj = os.path.join(OBJ, name + ".o")
         objs.append(obj)
         stale = force or not os.path.exists(obj) or any(
             os.path.getmtime(d) > os.path.getmtime(obj) for d in _deps(src))
+        if name == "capi.cu":
+            # carries the hash of ALL sources: rebuilt whenever that changes
+            extra = extra + [f'-DSAGE_SRC_HASH="{digest}"']
+            stale = stale or not os.path.exists(stamp) or open(stamp).read() != digest
         if stale:
             cmd = [_nvcc(), "-c", src, "-o", obj] + ARCH + COMMON + extra
             if verbose:
@@ -62,6 +82,8 @@ def build(force=False, verbose=False):
             raise RuntimeError(f"nvcc failed on {name}")
         if verbose:
             print(out)
+    with open(stamp, "w") as fh:
+        fh.write(digest)
     if rebuilt or not os.path.exists(LIB):
         cmd = [_nvcc(), "-shared", "-o", LIB] + objs + ARCH
         p = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)

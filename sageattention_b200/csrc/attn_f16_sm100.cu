@@ -52,6 +52,13 @@ using namespace sage;
 #ifndef SAGE_FUSE
 #define SAGE_FUSE 1
 #endif
+// 1: S_t(j+1) is issued in two N = 64 halves.  An f16 P row occupies only columns [0, 64) of the consumed S_t, so the
+// UPPER half of the next S (keys 64..127 -> columns [64, 128)) can go out as soon as the warpgroup has pulled S_t(j)
+// into registers (s_free barrier) and runs under the softmax; only the lower half waits for P.V(j), which takes
+// 128 cycles of Q.K^T off the P -> S critical path of every step.
+#ifndef SAGE_SSPLIT
+#define SAGE_SSPLIT 0
+#endif
 
 template <int D, bool kFp8>
 struct SmemLayout {
@@ -66,7 +73,7 @@ struct SmemLayout {
   static constexpr int kOBytes = kTileQ * D * 2;  // output staging tile per warpgroup: D/64 blocks of [128][128 B], SW128
   static constexpr int kOOff = kPOff + 2 * kPBytes;
   static constexpr int kBarOff = kOOff + 2 * kOBytes;
-  static constexpr int kNumBars = 2 * kQStages + 2 * kKStages + 2 * kVStages + 3 * 2 + 2 * 3 /*work ring*/;
+  static constexpr int kNumBars = 2 * kQStages + 2 * kKStages + 2 * kVStages + 4 * 2 + 2 * 3 /*work ring*/;
   static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
   static constexpr int kRingOff = kTmemPtrOff + 16;  // work ring: kSchedSlots x 16 B
   static constexpr int kVsOff = kRingOff + 4 * 16;    // v_scale [D] f32 of every ring slot (bulk-copied by the producer)
@@ -78,7 +85,7 @@ struct SmemLayout {
 template <int D, bool kFp8, bool kMask, bool kVarlen = false>
 __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, int row,
                                               const ItemCtx& c, const WorkItem* ring, uint32_t it,
-                                              uint32_t tmem_base, uint64_t* s_full, uint64_t* p_full,
+                                              uint32_t tmem_base, uint64_t* s_full, uint64_t* s_free, uint64_t* p_full,
                                               WgState& st, float& m_out, float& d_out) {
   const int warp_in_wg = (row >> 5);
   const uint32_t lane_off = (uint32_t)(warp_in_wg * 32) << 16;
@@ -157,6 +164,11 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
       tmem_ld32(tS + 64, s2);
       tmem_ld32(tS + 96, s3);
       tc_wait_ld();
+      if (SAGE_SSPLIT) {
+        // S_t is in registers: its upper 64 columns are free for the next S (P only uses the lower 64)
+        tc_fence_before();
+        mbar_arrive(&s_free[t]);
+      }
     }
     SAGE_STAMP(t, st.steps, 2);
     if (p.debug_s != nullptr && j == 0) {
@@ -288,7 +300,8 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   uint64_t* s_full = v_empty + kVStages;      // 2
   uint64_t* p_full = s_full + 2;              // 2
   uint64_t* o_full = p_full + 2;              // 2
-  uint64_t* sched_full = o_full + 2;          // kSchedSlots
+  uint64_t* s_free = o_full + 2;              // 2 (SAGE_SSPLIT)
+  uint64_t* sched_full = s_free + 2;          // kSchedSlots
   uint64_t* sched_empty = sched_full + kSchedSlots;
   WorkItem* ring = reinterpret_cast<WorkItem*>(smem + L::kRingOff);
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(smem + L::kTmemPtrOff);
@@ -303,6 +316,7 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       mbar_init(&s_full[t], 1);
       mbar_init(&p_full[t], kTileQ);
       mbar_init(&o_full[t], 1);
+      mbar_init(&s_free[t], kTileQ);
     }
     for (int i = 0; i < kSchedSlots; ++i) {
       mbar_init(&sched_full[i], 1);
@@ -341,7 +355,7 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     while (c.valid) {
       float m_run = 0.f, d_run = 1.f;
       if (c.n_iter > 0)
-        softmax_steps<D, kFp8, kMask, kVarlen>(p, t, row, c, ring, it, tmem_base, s_full, p_full, st, m_run,
+        softmax_steps<D, kFp8, kMask, kVarlen>(p, t, row, c, ring, it, tmem_base, s_full, s_free, p_full, st, m_run,
                                d_run);
       // the next item is prepared under this item's last P.V
       const bool had_steps = c.n_iter > 0;
@@ -452,6 +466,19 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         }
         tc_commit(&s_full[t]);
       };
+      // SAGE_SSPLIT: the two N = 64 halves of S_t (hi: keys 64..127 -> columns [64, 128); lo: keys 0..63)
+      constexpr uint32_t idesc_qk_half = make_idesc(CFMT_S32, FMT_S8, FMT_S8, 0, 0, kTileQ, kTileKV / 2);
+      uint32_t ns[2] = {0, 0};          // S_t issued so far (whole or split)
+      auto issue_qk_half = [&](int t, uint32_t qb, int hi) {
+        const uint32_t a0 = sQ + (qb * 2 + t) * L::kQBytes;
+        const uint32_t b0 = sK + (kc % kKStages) * L::kKBytes + (hi ? (kTileKV / 2) * D : 0);
+#pragma unroll
+        for (int kk = 0; kk < D / 32; ++kk) {
+          const uint64_t ad = make_smem_desc(a0 + kk * 32, 16, qk_sbo, qk_swz);
+          const uint64_t bd = make_smem_desc(b0 + kk * 32, 16, qk_sbo, qk_swz);
+          mma_i8_ss(tmem_base + t * 128 + (hi ? 64 : 0), ad, bd, idesc_qk_half, kk > 0);
+        }
+      };
       auto issue_pv = [&](int t, bool accumulate) {
         mbar_wait(&p_full[t], np[t] & 1u);
         tc_fence_after();
@@ -488,7 +515,7 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
           tc_fence_after();
 #pragma unroll
           for (int t = 0; t < 2; ++t)
-            if (n_it[t] > 0) issue_qk(t, 0);
+            if (n_it[t] > 0) { issue_qk(t, 0); ++ns[t]; }
           tc_commit(&k_empty[0]);
           ++kc;
           if (max(n_it[0], n_it[1]) == 1) tc_commit(&q_empty[0]);
@@ -514,6 +541,17 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
             mbar_wait(&k_full[kc % kKStages], (kc / kKStages) & 1u);
             tc_fence_after();
           }
+          if (SAGE_SSPLIT && (more || cross)) {
+            // upper halves of the next S first: they only need the warpgroup to have drained the current S
+#pragma unroll
+            for (int t = 0; t < 2; ++t) {
+              if (jn < (t == 0 ? nn0 : nn1)) {
+                if (ns[t] > 0) mbar_wait(&s_free[t], (ns[t] - 1) & 1u);
+                tc_fence_after();
+                issue_qk_half(t, qn, 1);
+              }
+            }
+          }
 #pragma unroll
           for (int t = 0; t < 2; ++t) {
             if (j < n_it[t]) {
@@ -521,7 +559,15 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
               if (j == n_it[t] - 1) tc_commit(&o_full[t]);
             }
             if (t == 1) tc_commit(&v_empty[vc % kVStages]);
-            if ((more || cross) && jn < (t == 0 ? nn0 : nn1)) issue_qk(t, qn);
+            if ((more || cross) && jn < (t == 0 ? nn0 : nn1)) {
+              if (SAGE_SSPLIT) {
+                issue_qk_half(t, qn, 0);
+                tc_commit(&s_full[t]);
+              } else {
+                issue_qk(t, qn);
+              }
+              ++ns[t];
+            }
           }
           ++vc;
           if (more || cross) {

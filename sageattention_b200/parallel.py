@@ -264,6 +264,10 @@ def ulysses_sageattn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, group=No
         raise ValueError(f"head counts ({h}, {k.size(2)}) must be divisible by the world size {world}")
     if q.size(0) == 1 and k.size(0) == 1 and all(t.is_contiguous() for t in (q, k, v)):
         # the DiT case (B = 1): communication pipelined against attention over groups of heads
+        if transport == "p2p" and (k.size(1) != q.size(1) or v.size(1) != k.size(1)):
+            # the peer-memory path lays its arena out for ONE sequence-shard length (q, k, v alike); cross attention
+            # with another kv length takes the NCCL path, which derives the length per tensor (round-1 ADVICE)
+            transport = "nccl"
         if transport == "p2p":
             if not q.is_cuda:
                 raise ValueError("transport='p2p' needs CUDA tensors")
