@@ -440,3 +440,26 @@ def test_capped_persistent_grid_is_bit_identical(pv, causal):
             core.GRID_LIMIT = None
         torch.cuda.synchronize()
         assert torch.equal(o, full), cap
+
+
+@pytest.mark.parametrize("fn", ["sageattn", "sageattn_qk_int8_pv_fp16_cuda"])
+def test_public_api_in_cuda_graph(fn):
+    """The operators' default path (one foreign call, one workspace from torch's graph-aware allocator, scheduler counter
+    zeroed by a captured memset) can be captured and replayed; a replay on new input values in the same buffers gives what
+    an eager call gives."""
+    q, k, v = make_qkv(1, 8, 4, 1024, 1024, 128, torch.bfloat16, seed=3)
+    f = getattr(sb, fn)
+    s = torch.cuda.Stream()
+    s.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(s):
+        f(q, k, v, is_causal=True)
+    torch.cuda.current_stream().wait_stream(s)
+    g = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g):
+        o = f(q, k, v, is_causal=True)
+    q2, k2, v2 = make_qkv(1, 8, 4, 1024, 1024, 128, torch.bfloat16, seed=4)
+    for a, b_ in ((q, q2), (k, k2), (v, v2)):
+        a.copy_(b_)
+    g.replay()
+    torch.cuda.synchronize()
+    assert torch.equal(o, f(q2, k2, v2, is_causal=True))
