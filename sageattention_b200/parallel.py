@@ -63,6 +63,23 @@ def _a2a_heads_in(x: torch.Tensor, lo: int, hi: int, group, world: int) -> torch
     return recv.view(1, world * n, hi - lo, d)
 
 
+def _a2a_heads_in_qkv(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, lo: int, hi: int, group, world: int):
+    """q, k, v of equal shape (no GQA): ONE all-to-all for all three instead of three.  The send buffer is laid out
+    [rank, token, (q|k|v), head, d], so in the receive buffer every tensor is a strided [1, n_loc*P, hi-lo, D] view with
+    a uniform token stride of 3*(hi-lo)*D - which the kernels take as it is (their TMA maps are built from the real
+    strides).  Same number of gather copies as the three-call path (one per tensor), two collective launches fewer."""
+    _, n, h, d = q.shape
+    hp = h // world
+    hc = hi - lo
+    send = torch.empty((world, n, 3, hc, d), dtype=q.dtype, device=q.device)
+    for i, x in enumerate((q, k, v)):
+        send[:, :, i].copy_(x.view(n, world, hp, d)[:, :, lo:hi].transpose(0, 1))
+    recv = torch.empty_like(send)
+    dist.all_to_all_single(recv, send, group=group)
+    r = recv.view(1, world * n, 3, hc, d)
+    return r[:, :, 0], r[:, :, 1], r[:, :, 2]
+
+
 def _a2a_heads_out(o: torch.Tensor, group, world: int) -> torch.Tensor:
     """Batch-1 path back: [1, n_loc*P, hc, D] (contiguous: it is its own send buffer, chunk p = sequence
     block p) -> [P, n_loc, hc, D], chunk p = these heads as computed by rank p."""
@@ -73,6 +90,8 @@ def _a2a_heads_out(o: torch.Tensor, group, world: int) -> torch.Tensor:
 
 
 _COMM_STREAMS = {}
+# B = 1, equal q / k / v shapes: one inbound all-to-all for q, k and v (strided views of one receive buffer) instead of three
+FUSED_QKV_A2A = True
 
 
 def _ulysses_b1(q, k, v, group, world, attn_fn, head_chunks, kwargs):
@@ -96,14 +115,21 @@ def _ulysses_b1(q, k, v, group, world, attn_fn, head_chunks, kwargs):
     ins = []
     for c in range(chunks):
         lo, hi = bounds[c], bounds[c + 1]
+        fused = FUSED_QKV_A2A and g == 1 and k.shape == q.shape and v.shape == q.shape
         if cuda:
             with torch.cuda.stream(comm):
-                t = tuple(_a2a_heads_in(x, a, b_, group, world)
-                          for x, a, b_ in ((q, lo * g, hi * g), (k, lo, hi), (v, lo, hi)))
+                if fused:
+                    t = _a2a_heads_in_qkv(q, k, v, lo, hi, group, world)
+                else:
+                    t = tuple(_a2a_heads_in(x, a, b_, group, world)
+                              for x, a, b_ in ((q, lo * g, hi * g), (k, lo, hi), (v, lo, hi)))
                 ev = torch.cuda.Event()
                 ev.record(comm)
             for x in t:
                 x.record_stream(cur)
+        elif fused:
+            t = _a2a_heads_in_qkv(q, k, v, lo, hi, group, world)
+            ev = None
         else:
             t = (_a2a_heads_in(q, lo * g, hi * g, group, world), _a2a_heads_in(k, lo, hi, group, world),
                  _a2a_heads_in(v, lo, hi, group, world))
