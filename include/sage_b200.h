@@ -166,6 +166,13 @@ int sage_per_channel_fp8(sage_tensor4 v, uint8_t* v_out, int64_t vo_stride_b, in
                          int n_stat, int D, int dtype, float scale_max, int smooth_v, void* workspace,
                          void* stream);
 
+/* sage_per_channel_fp8 with smooth_v = 0 as two flat launches (streaming channel range, then the conversion tiles) instead
+ * of one cluster per (b, h) slice; same outputs.  For long sequences of few heads (sequence-parallel DiT shards) the
+ * cluster launch leaves most SMs idle; sage_sageattn_fwd switches to this above 65 536 kv rows.  Same workspace. */
+int sage_per_channel_fp8_flat(sage_tensor4 v, uint8_t* v_out, int64_t vo_stride_b, int64_t vo_stride_h,
+                              int64_t vo_stride_d, float* v_scale, int B, int H, int N, int n_stat, int D, int dtype,
+                              float scale_max, void* workspace, void* stream);
+
 /* Attention kernels.  q8/k8: int8 [B,H,N,D] via strides; scales laid out exactly as the reference
  * quantizers produce them; o: f16/bf16 via strides; lse: [B,Hq,Nq] fp32 or NULL (base-2, as the
  * reference kernels return it). */

@@ -185,7 +185,8 @@ def _launch(fp8, q_int8, k_int8, v, o, q_scale, k_scale, v_scale, v_mean, tensor
 
 # One foreign call + one workspace per operator call (sage_sageattn_fwd) on the default paths; False = the two-call
 # path with one tensor per intermediate (kept for the non-default options and as the reference the fast path is
-# tested against: results are bit-identical).
+# tested against: results are bit-identical up to 65 536 kv rows; above, the library issues the prologue as flat
+# launches - faster for a few long slices - whose K mean can differ from the cluster kernel's in the last bit).
 FUSED_CALL = True
 _WS_BYTES = {}
 

@@ -4,8 +4,9 @@
 //   sageattn_qk_int8_pv_fp16_cuda             (/root/reference/sageattention/core.py:480-653: smooth_k, no smooth_v)
 // The reference's Python makes 6-8 allocations and 3-5 extension calls per operator call; the binding of round 1 made
 // 6-8 allocations and 2 calls (about 75 us of host time, more than the kernels take at N <= 2K).  Here the host side is
-// two allocations (workspace, output) and one foreign call.  It launches exactly what the separate entry points launch
-// (it calls them), so results are bit-identical to the two-call path.
+// two allocations (workspace, output) and one foreign call.  Up to kFlatPrologueRows kv rows it launches exactly what the
+// two-call path launches (it calls the same entry points), so results are bit-identical to it; above, the prologue is
+// issued as flat launches (below), whose K mean may differ from the cluster kernel's in the last bit of a channel.
 #include <cuda_runtime.h>
 #include <cstdint>
 
@@ -16,9 +17,18 @@ namespace {
 
 inline size_t align256(size_t x) { return (x + 255) & ~size_t(255); }
 
+// Above this many kv rows the prologue is issued as flat launches (K mean, Q quantiser, K quantiser, V range + conversion)
+// instead of the one-launch cluster prologue: a cluster of 8 CTAs owns a whole (b, h) slice, which is the right shape for
+// many short slices but leaves most SMs idle on a few long ones (a sequence-parallel DiT shard: 5 heads x 75 600 rows =
+// 40 CTAs per tensor; measured 352 -> 113 us for Q/K there, 805 -> 646 us with all 40 heads on one GPU), and beyond 64 K
+// rows the slices in flight no longer fit L2, so the second read of K comes from HBM either way.  The choice depends on
+// the sequence length ONLY, so a head-sharded run takes the same path - and gets the same bits - as the one-GPU run.
+constexpr int kFlatPrologueRows = 65536;
+
 struct Plan {
-  size_t q8, k8, qs, ks, km, v, vs, total;   // byte offsets into the workspace
+  size_t q8, k8, qs, ks, km, v, vs, stat, zmean, total;   // byte offsets into the workspace
   int q_per_bh, k_per_bh, npad;
+  bool flat;
 };
 
 Plan make_plan(const sage_fwd_args* a) {
@@ -40,6 +50,18 @@ Plan make_plan(const sage_fwd_args* a) {
   else if (a->dtype == SAGE_DTYPE_BF16) off = align256(off + B * Hkv * Nk * d_og * 2);   // the f16 copy of a bf16 V
   p.vs = off;
   if (a->pv_fp8) off = align256(off + B * Hkv * D * 4);
+  p.flat = a->Nk > kFlatPrologueRows && d_og == (size_t)a->D;
+  p.stat = p.zmean = off;
+  if (p.flat) {
+    size_t need = sage_seq_mean_workspace_bytes(a->B, a->Hkv, a->Nk, a->D);
+    if (a->pv_fp8) {
+      const size_t nv = sage_per_channel_fp8_workspace_bytes(a->B, a->Hkv, a->Nk, a->D);
+      if (nv > need) need = nv;
+    }
+    off = align256(off + need);
+    p.zmean = off;
+    if (!a->pv_fp8 && a->dtype == SAGE_DTYPE_BF16) off = align256(off + B * Hkv * D * 2);
+  }
   p.total = off;
   return p;
 }
@@ -104,7 +126,46 @@ extern "C" int sage_sageattn_fwd(const sage_fwd_args* a, void* stream) {
   at.d_og = d_og != a->D ? d_og : 0;
   at.max_ctas = a->max_ctas;
 
-  if (a->pv_fp8) {
+  if (p.flat) {
+    // ---- long sequences: flat launches (see kFlatPrologueRows)
+    void* stat = ws + p.stat;
+    rc = sage_seq_mean(a->k, km, a->B, a->Hkv, a->Nk, a->D, a->dtype, stat, stream);
+    if (rc) return rc;
+    if (a->per_thread) {
+      rc = sage_quant_per_thread_int8(a->q, nullptr, q8, q_scale, a->B, a->Hq, a->Nq, a->D, a->dtype, 0, a->warp_q, stream);
+      if (rc) return rc;
+      rc = sage_quant_per_thread_int8(a->k, km, k8, k_scale, a->B, a->Hkv, a->Nk, a->D, a->dtype, 1, 64, stream);
+    } else {
+      rc = sage_quant_int8(a->q, nullptr, q8, q_scale, a->B, a->Hq, a->Nq, a->D, a->dtype, a->warp_q, p.q_per_bh, 0, 0.f, stream);
+      if (rc) return rc;
+      rc = sage_quant_int8(a->k, km, k8, k_scale, a->B, a->Hkv, a->Nk, a->D, a->dtype, 64, p.k_per_bh, 0, 0.f, stream);
+    }
+    if (rc) return rc;
+    if (a->pv_fp8) {
+      uint8_t* v8 = ws + p.v;
+      float* v_scale = reinterpret_cast<float*>(ws + p.vs);
+      const int64_t np = p.npad;
+      const int64_t sb = (int64_t)a->Hkv * a->D * np;
+      const int64_t sh = hnd ? a->D * np : np;
+      const int64_t sd = hnd ? np : (int64_t)a->Hkv * np;
+      rc = sage_per_channel_fp8_flat(a->v, v8, sb, sh, sd, v_scale, a->B, a->Hkv, a->Nk, p.npad, a->D, a->dtype,
+                                     a->v_scale_max, stat, stream);
+      if (rc) return rc;
+      at.v.ptr = v8; at.v.stride_b = sb; at.v.stride_h = sh; at.v.stride_n = sd;
+      at.v_scale = v_scale;
+      at.npad_v = p.npad;
+    } else if (a->dtype == SAGE_DTYPE_BF16) {
+      // the f16 copy of a bf16 V: half(v - 0) is the exact cast (the packed subtraction of zero is the identity)
+      sage_tensor4 v16 = make_t4(ws + p.v, hnd, a->Hkv, a->Nk, d_og);
+      void* zero = ws + p.zmean;
+      SAGE_CUDA(cudaMemsetAsync(zero, 0, (size_t)a->B * a->Hkv * a->D * 2, st));
+      rc = sage_sub_mean(a->v, zero, v16, a->B, a->Hkv, a->Nk, a->D, a->dtype, stream);
+      if (rc) return rc;
+      at.v = v16;
+    } else {
+      at.v = a->v;
+    }
+  } else if (a->pv_fp8) {
     // v_fp8: [B,Hkv,D,Npad] (HND) or [B,D,Hkv,Npad] (NHD), as the two-call path allocates it
     uint8_t* v8 = ws + p.v;
     float* v_scale = reinterpret_cast<float*>(ws + p.vs);

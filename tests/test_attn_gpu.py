@@ -463,3 +463,59 @@ def test_public_api_in_cuda_graph(fn):
     g.replay()
     torch.cuda.synchronize()
     assert torch.equal(o, f(q2, k2, v2, is_causal=True))
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("layout", ["HND", "NHD"])
+def test_flat_v_conversion_equals_cluster_launch(dtype, layout):
+    """sage_per_channel_fp8_flat (streaming channel range + flat conversion tiles; used by sage_sageattn_fwd above 65 536 kv
+    rows) gives the codes and scales of the one-launch cluster kernel, bit for bit."""
+    b, h, n, d = 2, 3, 5003, 128
+    g = torch.Generator(device=DEV).manual_seed(9)
+    v = (torch.randn(b, h, n, d, generator=g, device=DEV) * 3).to(dtype)
+    if layout == "NHD":
+        v = v.transpose(1, 2).contiguous()
+    n_stat = (n + 127) // 128 * 128
+    ref8, refs, _ = sb.per_channel_fp8(v, tensor_layout=layout, scale_max=448.0, smooth_v=False, _n_stat=n_stat)
+    lib = _lib.load()
+    from sageattention_b200.quant import _dims, _dtype_code, _stream
+    _, _, _, _, v4 = _dims(v, layout)
+    out = torch.empty_like(ref8)
+    vs = torch.empty_like(refs)
+    if layout == "HND":
+        sb_, sh_, sd_ = out.stride(0), out.stride(1), out.stride(2)
+    else:
+        sb_, sh_, sd_ = out.stride(0), out.stride(2), out.stride(1)
+    ws = torch.empty(lib.sage_per_channel_fp8_workspace_bytes(b, h, n, d), dtype=torch.uint8, device=DEV)
+    _lib.check(lib.sage_per_channel_fp8_flat(v4, out.data_ptr(), sb_, sh_, sd_, vs.data_ptr(), b, h, n, n_stat, d,
+                                             _dtype_code(v), 448.0, ws.data_ptr(), _stream(v)))
+    torch.cuda.synchronize()
+    assert torch.equal(vs, refs)
+    assert torch.equal(out.view(torch.uint8), ref8.view(torch.uint8))
+
+
+@pytest.mark.parametrize("fn", ["sageattn", "sageattn_qk_int8_pv_fp16_cuda"])
+def test_long_sequence_flat_prologue(fn):
+    """Above 65 536 kv rows sage_sageattn_fwd issues the prologue as flat launches.  The result must (a) agree with the
+    two-call (cluster prologue) path to within the effect of a last-bit difference in the K mean, (b) not depend on which
+    heads share the launch - the path is chosen from the sequence length alone, which is what keeps a head-sharded
+    (Ulysses) run bit-identical to the one-GPU run - and (c) still be attention (sampled rows against fp32)."""
+    b, h, n, d = 1, 4, 66000, 128
+    q, k, v = make_qkv(b, h, h, n, n, d, torch.bfloat16, seed=29)
+    f = getattr(sb, fn)
+    o = f(q, k, v)
+    core.FUSED_CALL = False
+    try:
+        o2 = f(q, k, v)
+    finally:
+        core.FUSED_CALL = True
+    cos, l1, _ = accuracy(o, o2)
+    assert cos >= 0.99999 and l1 <= 2e-3, (cos, l1)
+    o_half = f(q[:, 1:3].contiguous(), k[:, 1:3].contiguous(), v[:, 1:3].contiguous())
+    torch.cuda.synchronize()
+    assert torch.equal(o_half, o[:, 1:3])
+    rows = torch.linspace(0, n - 1, 256).long().to(DEV)
+    s = (q[0, 3, rows].float() @ k[0, 3].float().t()) * d ** -0.5
+    ref = torch.softmax(s, -1) @ v[0, 3].float()
+    cos, l1, _ = accuracy(o[0, 3, rows], ref)
+    assert cos >= 0.999 and l1 <= (5e-2 if fn == "sageattn" else 1.5e-2), (cos, l1)
