@@ -23,8 +23,8 @@ COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-w", f"-I{os
 UNITS = [
     ("capi.cu", []),
     ("prepass.cu", ["--use_fast_math"]),
-    ("attn_sm100.cu", []),
     ("attn_f16_sm100.cu", []),
+    ("attn_f8_sm100.cu", []),
     ("fwd.cu", []),
 ]
 

@@ -1,8 +1,8 @@
-// Shared by the two attention translation units (attn_sm100.cu: P through shared memory / spare TMEM columns;
-// attn_f16_sm100.cu: f16 P over S in TMEM at head_dim 128): kernel parameters, the persistent work list with its
-// dynamic scheduler, the per-item set-up and epilogue of the softmax warpgroups, and the host-side helpers
-// (TMA descriptors, per-device state, argument checks).  The step loops, the MMA issuers, the kernels and their
-// launchers differ and stay in the .cu files.  Everything here has internal linkage or is a template / inline.
+// Support code of the attention kernel (attn_kernel_sm100.cuh, instantiated by attn_f16_sm100.cu and attn_f8_sm100.cu):
+// kernel parameters, the persistent work list with its dynamic scheduler, the per-item set-up and epilogue of the softmax
+// warpgroups, and the host-side helpers (TMA descriptors, per-device state, argument checks).  The step loop, the MMA
+// issuer, the kernel and its launcher are in attn_kernel_sm100.cuh.  Everything here has internal linkage or is a
+// template / inline.
 #pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>

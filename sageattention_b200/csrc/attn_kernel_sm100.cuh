@@ -1,34 +1,30 @@
-// SageAttention forward for sm_100a (B200), FP8 P.V flavour: INT8 QK^T + online softmax + e4m3 P.V
-// (sage_attn_i8_f8; the f16 P.V entry point lives in attn_f16_sm100.cu)
+// SageAttention forward for sm_100a (B200): INT8 QK^T + online softmax + P.V in f16 or e4m3, ONE kernel template
+//   sage_attn_fwd_kernel<D, kFp8, kMask, kVarlen>     D = 64 | 128, P.V in e4m3 (kFp8) or f16
+// instantiated by attn_f16_sm100.cu (sage_attn_i8_f16) and attn_f8_sm100.cu (sage_attn_i8_f8).
 //
-// Replaces the reference's mma.sync kernels
+// Replaces the reference's mma.sync / wgmma kernels
 //   qk_int_sv_f16_attn_kernel  (/root/reference/csrc/qattn/qk_int_sv_f16_cuda_sm80.cu:44-671)
-//   qk_int_sv_f8_attn_kernel   (/root/reference/csrc/qattn/qk_int_sv_f8_cuda_sm89.cuh:44-707)
-// with a from-scratch tcgen05 design (not a port):
-//
-//   * PERSISTENT grid (one CTA per SM): a work item is TWO 128-row Q tiles (256 query rows) of one
-//     (batch, head), walked over the KV sequence in 128-row tiles; items come from a dynamic scheduler
-//     (attn_common_sm100.cuh), barrier phases run on across items, and the issuer launches the next
-//     item's first Q.K^T under the current item's last step and epilogue;
-//   * warp 8 is the TMA producer (a Q ring of two items, a K ring and a V ring, 128B-swizzled smem);
-//   * warp 9 is the single-thread MMA issuer:  S_t = Q_t.K^T  as tcgen05.mma kind::i8 (s32 in TMEM),
-//     O_t += P_t.V as kind::f8f6f4 (e4m3) or kind::f16, P read from shared memory;
-//   * warps 0-3 / 4-7 are two softmax warpgroups, one per Q tile, one thread per query row:
-//     tcgen05.ld S (whole row to registers, which frees S_t at once) -> dequant (q/k scales) ->
-//     running max / exp2 / row-sum -> P packed to e4m3/f16 and written to a 128B-swizzled smem tile;
-//     they also rescale O in TMEM when a row maximum moves by more than tau, and run the epilogue
-//     (1/d, v_scale, v_mean, cast, store, LSE).
-//   Because P does not alias S, the issuer launches S_t(j+1) as soon as warpgroup t has drained
-//   S_t(j): the QK MMA runs under that warpgroup's own softmax and the warpgroups never wait for
-//   the tensor pipe in steady state (measured: tools/trace_attn.py).
+//   qk_int_sv_f8_attn_kernel   (/root/reference/csrc/qattn/qk_int_sv_f8_cuda_sm89.cuh:44-..., ..._sm90.cu)
+// with a from-scratch tcgen05 design: persistent grid (one CTA per SM) with a dynamic work scheduler, two 128-row Q
+// tiles per work item, a TMA producer warp, a single-thread MMA issuer, two softmax warpgroups with one thread per
+// query row, lazy O rescale, setmaxnreg 232/40, TMA-store epilogue.
 //
 // TMEM map (512 columns):  S0 [0,128)  S1 [128,256)  O0 [256,256+D)  O1 [256+D,256+2D).
+// P_t is written back over the consumed S_t columns with tcgen05.st (f16: columns [0,64), e4m3: [0,32)) and read by the
+// P.V MMA as its TMEM A operand.  The P -> S dependency this aliasing creates (S_t(j+1) cannot overtake the P.V that
+// still reads P_t(j); the tensor pipe executes in order) is taken off the critical path in two ways (round 2, measured
+// +8..14 % on every configuration; see SAGE_PSPLIT / SAGE_SSPLIT below and tools/experiments/README.md):
+//   * P goes out in two parts, so most of P.V(j) runs under the tail of the exp window;
+//   * S(j+1) is issued as two N = 64 halves, the upper one ahead of P.V(j), and the warpgroup works on it while the
+//     lower one is still being computed.
+// Until then the e4m3 and head_dim-64 flavours used a second kernel (P through shared memory / spare TMEM columns, exp
+// windows of the two warpgroups alternating; attn_sm100.cu in the history) - this one now beats it everywhere.
 //
-// Numerics contract (tolerance-checked against the reference kernels and fp32 SDPA):
-//   s' = S * q_scale * k_scale * sm_scale * log2(e);  m = running row max;  p = ex2(s' - m [+8.807]);
-//   d = sum of f32 p;  O = sum p.v (f32 in TMEM);  out = O / d [* v_scale] [+ v_mean];
-//   lse = log2(d) + m [- 8.807]   (base 2, as the reference kernels return it).
-//   Masked entries (causal kv > q, kv >= kv_len) contribute exactly 0.
+// Numerics contract: logits dequantised as s * (q_scale * k_scale[class] * sm_scale * log2 e); online softmax in base 2
+// with a lazily rescaled accumulator (tau = 8 for f16 P, 2 for e4m3 P, whose exponent carries the reference's +8.807
+// offset, attn_utils.cuh:30); P rounded to f16 / e4m3 (rn, satfinite), P.V accumulated in fp32 in TMEM over the WHOLE
+// kv sequence (the reference's sm89 kernel accumulates in fp32 across 32 MMAs and then in registers; sm90 in fp32).
+#pragma once
 #include <cuda.h>
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
@@ -41,44 +37,73 @@
 
 #include "attn_common_sm100.cuh"
 
-namespace sage {
+namespace sage_attn {
+using namespace sage;
 
-// 1 = the exp phases of the two softmax warpgroups alternate (named barriers), 0 = free-running.
-// (Whole-step alternation, a fixed phase offset and pre-biased S were measured slower and live in
-// tools/experiments/attn_v0e_f8_per_item_grid.cu.)
+// The two softmax warpgroups run freely here (alternating their exp phases was measured slower with P
+// in TMEM).
 #ifndef SAGE_TURN
-#define SAGE_TURN 1
+#define SAGE_TURN 0
 #endif
-// 1: S(j+1) is pulled into registers under the P store's fence of step j instead of at the top of step
-// j+1.  Measured 6 % SLOWER (hd128 1288 -> 1211, hd64 674 -> 623 TOPS at N=8192), default 0.
-#ifndef SAGE_SPREF
-#define SAGE_SPREF 0
-#endif
-// k scales of later steps prefetched to L1: measured -0.7 %, off.
-#ifndef SAGE_KPREF
-#define SAGE_KPREF 0
-#endif
-
-// 1: the unmasked row maximum as depth-3 trees of 3-input maxima (40 independent first-level operations)
 #ifndef SAGE_MAXTREE
 #define SAGE_MAXTREE 0
 #endif
-// 1: the k scales of a kv step as two 16-byte loads (per_thread) / two scalars (per_warp) instead of eight indexed loads.
-// Measured (one box, kernel-only, N = 8K / 32K): +3 % in the f16 hd128 kernel (attn_f16_sm100.cu: 1253 -> 1299 / 1161 ->
-// 1198 TOPS, where it is on) but -2 % (fp8 hd128: 1304 -> 1283) and -5 % (fp8 hd64: 679 -> 648) here, so off.
+// 1: the k scales of a kv step as two 16-byte loads (per_thread) / two scalars (per_warp) instead of eight indexed loads
 #ifndef SAGE_KSVEC
-#define SAGE_KSVEC 0
+#define SAGE_KSVEC 1
 #endif
-// 0: exp, pack and store are separate phases.  1: the e4m3 / f16 conversions are issued group by group (16
-// columns) inside the exp phase, under the MUFU pipe.  2: as 1, and every group is stored (shared memory or
-// TMEM) as soon as it is packed, so that only the fence and the barrier arrival are left after the window.
+// f16 / e4m3 conversions issued group by group (16 columns) inside the exp phase, under the MUFU pipe.
+// Measured at f16 hd128 N=8192: 1183 (median; 1252 best, noisy) -> 1263 TOPS (stable).  It is also what lets P go out
+// in parts (SAGE_PSPLIT).
 #ifndef SAGE_FUSE
-#define SAGE_FUSE 0
+#define SAGE_FUSE 1
+#endif
+// 1: S_t(j+1) is issued in two N = 64 halves, each with its own barrier.  An f16 P row occupies only columns [0, 64) of
+// the consumed S_t, so the UPPER half of the next S (keys 64..127 -> columns [64, 128)) goes out as soon as the warpgroup
+// has pulled the upper half of S_t(j) into registers (s_free) - ahead of P.V(j) on the tensor pipe - and at the start of
+// step j+1 the warpgroup finds it ready: it loads it and takes its class maxima while P.V(j) (late part) and the lower
+// half of Q.K^T(j+1) are still running.  (Round 2's first form of this waited for both warpgroups' s_free before any
+// P.V and had one barrier for the whole S: -1 %.)
+#ifndef SAGE_SSPLIT
+#define SAGE_SSPLIT 1
 #endif
 
-// P_t in its own TMEM columns (head_dim 64: S 256 + O 128 + P 64/128 columns) or in shared memory
-template <int D>
-constexpr bool kPTmem = (D == 64);
+// n > 0: the P row goes out in two parts.  The first n groups of 16 columns are stored (and announced on p_part) while
+// the exponentials of the remaining groups are still running, so the first n K-steps of P.V(j) execute under the exp
+// window instead of after it; the rest follows on p_full as before.  The lazy O rescale then has to happen BEFORE the
+// window (its decision is known after the max phase).  SAGE_PSPLIT_LAG: groups computed between the early tcgen05.st and
+// the wait::st + arrive that publishes it.  Measured (burst TOPS, B4 H32, profiles/r2k_*): f16 hd128 N = 2K / 4K / 8K /
+// 8K causal 1140 / 1232 / 1272 / 1200 -> 1281 / 1392 / 1446 / 1325 with n = 6 and SAGE_SSPLIT; e4m3 hd128 (against the
+// former shared-memory-P kernel) 1169 / - / 1305 / 1217 -> 1257 / - / 1459 / 1335 with n = 4; hd64 e4m3 679 -> 738,
+// f16 678 -> 700.  Outputs are bit-identical to the unsplit kernel.
+#ifndef SAGE_PSPLIT
+#define SAGE_PSPLIT 6
+#endif
+#ifndef SAGE_PSPLIT_LAG
+#define SAGE_PSPLIT_LAG 0
+#endif
+
+#ifndef SAGE_PSPLIT_SMALL
+#define SAGE_PSPLIT_SMALL 4   // the e4m3 flavour and head_dim 64 (shorter P.V): measured best at 4
+#endif
+template <int D, bool kFp8>
+__host__ __device__ constexpr int psplit_groups() { return (kFp8 || D == 64) ? SAGE_PSPLIT_SMALL : SAGE_PSPLIT; }
+
+// words [kBegin, kEnd) of a packed P row -> TMEM columns tP + kBegin.. (multiples of 8 words)
+template <int kBegin, int kEnd, int kN>
+__device__ __forceinline__ void tmem_st_words(uint32_t tP, uint32_t (&w)[kN]) {
+  static_assert(kBegin % 8 == 0 && kEnd % 8 == 0 && kEnd <= kN, "8-word units");
+  if constexpr (kEnd - kBegin >= 32) {
+    tmem_st32(tP + kBegin, *reinterpret_cast<uint32_t(*)[32]>(&w[kBegin]));
+    tmem_st_words<kBegin + 32, kEnd>(tP, w);
+  } else if constexpr (kEnd - kBegin >= 16) {
+    tmem_st16(tP + kBegin, *reinterpret_cast<uint32_t(*)[16]>(&w[kBegin]));
+    tmem_st_words<kBegin + 16, kEnd>(tP, w);
+  } else if constexpr (kEnd - kBegin >= 8) {
+    tmem_st8(tP + kBegin, *reinterpret_cast<uint32_t(*)[8]>(&w[kBegin]));
+    tmem_st_words<kBegin + 8, kEnd>(tP, w);
+  }
+}
 
 template <int D, bool kFp8>
 struct SmemLayout {
@@ -88,12 +113,12 @@ struct SmemLayout {
   static constexpr int kQOff = 0;
   static constexpr int kKOff = kQOff + kQStages * 2 * kQBytes;
   static constexpr int kVOff = kKOff + kKStages * kKBytes;
-  static constexpr int kPBytes = kPTmem<D> ? 0 : (kFp8 ? kTileQ * kTileKV : kTileQ * kTileKV * 2);  // K-major, SW128
+  static constexpr int kPBytes = 0;  // P lives in TMEM
   static constexpr int kPOff = kVOff + kVStages * kVBytes;
   static constexpr int kOBytes = kTileQ * D * 2;  // output staging tile per warpgroup: D/64 blocks of [128][128 B], SW128
   static constexpr int kOOff = kPOff + 2 * kPBytes;
   static constexpr int kBarOff = kOOff + 2 * kOBytes;
-  static constexpr int kNumBars = 2 * kQStages + 2 * kKStages + 2 * kVStages + 5 * 2 + 2 * 3 /*work ring*/;
+  static constexpr int kNumBars = 2 * kQStages + 2 * kKStages + 2 * kVStages + 6 * 2 + 2 * 3 /*work ring*/;
   static constexpr int kTmemPtrOff = kBarOff + kNumBars * 8;
   static constexpr int kRingOff = kTmemPtrOff + 16;  // work ring: kSchedSlots x 16 B
   static constexpr int kVsOff = kRingOff + 4 * 16;    // v_scale [D] f32 of every ring slot (bulk-copied by the producer)
@@ -105,9 +130,8 @@ struct SmemLayout {
 template <int D, bool kFp8, bool kMask, bool kVarlen = false>
 __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, int row,
                                               const ItemCtx& c, const WorkItem* ring, uint32_t it,
-                                              uint32_t tmem_base, uint8_t* p_smem, uint64_t* s_full,
-                                              uint64_t* s_free, uint64_t* p_full, uint64_t* p_empty,
-                                              WgState& st, float& m_out, float& d_out) {
+                                              uint32_t tmem_base, uint64_t* s_full, uint64_t* s_free, uint64_t* p_full,
+                                              uint64_t* p_part, uint64_t* s_hi, WgState& st, float& m_out, float& d_out) {
   const int warp_in_wg = (row >> 5);
   const uint32_t lane_off = (uint32_t)(warp_in_wg * 32) << 16;
   const uint32_t tS = tmem_base + lane_off + (uint32_t)(t * 128);
@@ -123,7 +147,6 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
   // Only the first n_pingpong steps of an item, which both warpgroups execute, take part.  Warpgroup 1
   // grants warpgroup 0's first turn of an item either here or, when it can, right after its own last
   // exp phase of the previous item (so that warpgroup 0 does not wait for warpgroup 1's epilogue).
-  // (the attn_mask kernels run their warpgroups freely: kTurn = 0)
   constexpr int kTurn = kMask ? 0 : SAGE_TURN;
   if (kTurn != 0 && t == 1 && n_pingpong > 0) {
     if (!st.granted) named_bar_arrive(1, 2 * kTileQ);
@@ -133,26 +156,6 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
   const bool trace_on = blockIdx.x == 0 && row == 0;
 #endif
 
-  uint32_t s[128];
-  auto load_s = [&]() {
-    uint32_t(&s0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
-    uint32_t(&s1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[32]);
-    uint32_t(&s2)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[64]);
-    uint32_t(&s3)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[96]);
-    tmem_ld32(tS + 0, s0);
-    tmem_ld32(tS + 32, s1);
-    tmem_ld32(tS + 64, s2);
-    tmem_ld32(tS + 96, s3);
-  };
-#if SAGE_SPREF
-  // the first S of the item; every later one is pulled in under the previous step's P store
-  mbar_wait(&s_full[t], st.steps & 1u);
-  tc_fence_after();
-  load_s();
-  tc_wait_ld();
-  tc_fence_before();
-  mbar_arrive(&s_free[t]);  // S_t is in registers: the issuer may overwrite it with the next S_t
-#endif
   for (int j = 0; j < n_iter; ++j) {
     const uint32_t ph = st.steps & 1u;
     // k scales of this tile -> 8 class scales
@@ -191,19 +194,46 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
         sc[k] = __ldg(ksp + (size_t)idx * c.ks_stride) * qs;
       }
     }
-    // pull the next steps' k scales towards L1 (a 128-byte line holds 4 (per_thread) / 16 steps)
-    if (SAGE_KPREF) prefetch_l1(ksp + min((j + 2) * (p.gran == 3 ? 8 : 2), p.k_scale_per_bh - 1));
+    const int kv0 = j * kTileKV;
+    const int k_len = kVarlen ? c.k_len : p.Nk;
+    int lim = k_len - 1 - kv0;
+    if (p.causal) lim = min(lim, q_row - kv0);
+    const bool masked_tile = (j == n_iter - 1) && (p.causal || (k_len - kv0) < kTileKV);
     SAGE_STAMP(t, st.steps, 0);
-#if !SAGE_SPREF
-    mbar_wait(&s_full[t], ph);
-    tc_fence_after();
-    SAGE_STAMP(t, st.steps, 1);
-    load_s();
-    tc_wait_ld();
-    // S_t is in registers: the issuer may overwrite it with the next S_t
-    tc_fence_before();
-    mbar_arrive(&s_free[t]);
-#endif
+    uint32_t s[128];
+    int mx[8];
+    {
+      uint32_t(&s0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
+      uint32_t(&s1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[32]);
+      uint32_t(&s2)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[64]);
+      uint32_t(&s3)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[96]);
+      if (SAGE_SSPLIT) {
+        mbar_wait(&s_hi[t], ph);
+        tc_fence_after();
+        tmem_ld32(tS + 64, s2);
+        tmem_ld32(tS + 96, s3);
+        tc_wait_ld();
+        // the upper 64 columns of S_t are in registers and P will not use them: free for the next S
+        tc_fence_before();
+        mbar_arrive(&s_free[t]);
+        if (!kMask && !masked_tile) softmax_halfmax<1>(s, mx);
+        mbar_wait(&s_full[t], ph);
+        tc_fence_after();
+        SAGE_STAMP(t, st.steps, 1);
+        tmem_ld32(tS + 0, s0);
+        tmem_ld32(tS + 32, s1);
+        tc_wait_ld();
+      } else {
+        mbar_wait(&s_full[t], ph);
+        tc_fence_after();
+        SAGE_STAMP(t, st.steps, 1);
+        tmem_ld32(tS + 0, s0);
+        tmem_ld32(tS + 32, s1);
+        tmem_ld32(tS + 64, s2);
+        tmem_ld32(tS + 96, s3);
+        tc_wait_ld();
+      }
+    }
     SAGE_STAMP(t, st.steps, 2);
     if (p.debug_s != nullptr && j == 0) {
       const int nq_pad = (p.Nq + 255) / 256 * 256;
@@ -213,30 +243,51 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
 #pragma unroll
       for (int c = 0; c < 128; ++c) dst[c] = (int)s[c];
     }
-    const int kv0 = j * kTileKV;
-    const int k_len = kVarlen ? c.k_len : p.Nk;
-    int lim = k_len - 1 - kv0;
-    if (p.causal) lim = min(lim, q_row - kv0);
-    const bool masked_tile = (j == n_iter - 1) && (p.causal || (k_len - kv0) < kTileKV);
     float alpha, bias[8], dsum;
+    uint32_t w[kFp8 ? 32 : 64];
     if constexpr (kMask) {
       // attn_mask: max, exponentials and row sum of y = logit + mask in one call (softmax_sm100.cuh)
       dsum = softmax_general_mask<kFp8>(s, sc, lim, c.mask_row + (size_t)kv0 * (p.mask_kind == 1 ? 1 : 2), p.mask_kind,
                                         m_run, alpha);
     } else if (masked_tile) softmax_max<kFp8, true, false>(s, sc, lim, m_run, alpha, bias);
-    else if (SAGE_MAXTREE) softmax_max_tree<kFp8>(s, sc, m_run, alpha, bias);
+    else if (SAGE_SSPLIT) {
+      softmax_halfmax<0>(s, mx);
+      softmax_max_finish<kFp8>(mx, sc, m_run, alpha, bias);
+    } else if (SAGE_MAXTREE) softmax_max_tree<kFp8>(s, sc, m_run, alpha, bias);
     else softmax_max<kFp8, false, false>(s, sc, 127, m_run, alpha, bias);
+    // rescale O when some row of this warp moved its max (PV(j-1) is complete: S(j) was issued after
+    // it and tcgen05.commit tracks all earlier MMAs)
+    auto rescale_o = [&]() {
+      if (j > 0) {
+        if (__any_sync(0xffffffffu, alpha != 1.0f)) {
+#pragma unroll
+          for (int c0 = 0; c0 < D; c0 += 32) {
+            uint32_t o[32];
+            tmem_ld32(tO + c0, o);
+            tc_wait_ld();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st32(tO + c0, o);
+          }
+        }
+      }
+    };
+    constexpr int kPs = (kMask || SAGE_FUSE != 1) ? 0 : psplit_groups<D, kFp8>();   // groups in the early part of P
+    constexpr int kWg = kFp8 ? 4 : 8;                                  // packed words per 16-column group
+    static_assert(kPs >= 0 && kPs < 8 && (!kFp8 || kPs % 2 == 0), "SAGE_PSPLIT");
+    if constexpr (kPs > 0) rescale_o();   // before any part of P.V(j) may start
     SAGE_STAMP(t, st.steps, 5);
-    // shared-memory address of this row's P (K-major, 128B swizzle: 16B chunk c of row r sits at chunk c ^ (r & 7))
-    const uint32_t prow = smem_u32(p_smem) + (uint32_t)row * 128u;
-    const uint32_t px = (uint32_t)(row & 7);
-    const uint32_t tP = tmem_base + lane_off + (uint32_t)(384 + t * (kFp8 ? 32 : 64));  // kPTmem only
-#if SAGE_FUSE
-    // PV(j-1) complete: P tile reusable (checked before the window when the groups are stored inside it)
-    if (SAGE_FUSE == 2 && j > 0) mbar_wait(&p_empty[t], ph ^ 1u);
+    // The exp phases of the two warpgroups alternate (they are the only MUFU-bound stretch): each
+    // warpgroup's load / max / pack / store phases then run under the other one's exponentials.
     if (kTurn == 1 && j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
     SAGE_STAMP(t, st.steps, 6);
-    uint32_t w[kFp8 ? 32 : 64];  // (SAGE_FUSE == 2 reuses the first group's words)
+    constexpr int kFuse = kMask ? 0 : SAGE_FUSE;
+    if constexpr (kMask) {
+      // (exponentials done above)
+    } else {
+#if SAGE_FUSE
+    // conversions issued group by group (16 columns) under the MUFU pipe; SAGE_FUSE == 2 also stores every group
+    // over the consumed S columns as soon as it is packed
     auto window = [&](auto masked_c) {
       constexpr bool kM = decltype(masked_c)::value;
       uint64_t dsum2 = 0;
@@ -246,12 +297,15 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
         uint32_t(&wg)[kW] = *reinterpret_cast<uint32_t(*)[kW]>(&w[SAGE_FUSE == 2 ? 0 : g * kW]);
         softmax_exp_pack16<kFp8, kM>(g, s, sc, bias, kM ? lim : 127, dsum2, wg);
         if (SAGE_FUSE == 2) {
-          if constexpr (kPTmem<D>) {
-            if constexpr (kFp8) tmem_st4(tP + g * 4, *reinterpret_cast<uint32_t(*)[4]>(&wg[0]));
-            else tmem_st8(tP + g * 8, *reinterpret_cast<uint32_t(*)[8]>(&wg[0]));
-          } else {
-            // (this file's shared-memory P is e4m3: 16 columns = one 16-byte chunk)
-            st_shared_v4(prow + (((uint32_t)g ^ px) << 4), wg[0], wg[1], wg[2], wg[3]);
+          if constexpr (kFp8) tmem_st4(tS + g * 4, *reinterpret_cast<uint32_t(*)[4]>(&wg[0]));
+          else tmem_st8(tS + g * 8, *reinterpret_cast<uint32_t(*)[8]>(&wg[0]));
+        }
+        if constexpr (kPs > 0) {
+          if (g == kPs - 1) tmem_st_words<0, kPs * kWg>(tS, w);
+          if (g == (kPs - 1 + SAGE_PSPLIT_LAG < 7 ? kPs - 1 + SAGE_PSPLIT_LAG : 7)) {
+            tc_wait_st();
+            tc_fence_before();
+            mbar_arrive(&p_part[t]);
           }
         }
       }
@@ -261,29 +315,11 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
     };
     if (masked_tile) window(std::true_type{});
     else window(std::false_type{});
-    if (kTurn == 1 && j < n_pingpong) {
-      if (t == 0) {
-        named_bar_arrive(2, 2 * kTileQ);
-      } else if (j < n_pingpong - 1) {
-        named_bar_arrive(1, 2 * kTileQ);
-      } else if (next_pingpong) {
-        named_bar_arrive(1, 2 * kTileQ);
-        st.granted = true;
-      }
-    }
-    SAGE_STAMP(t, st.steps, 7);
-    d_run = fmaf(d_run, alpha, dsum);
-    SAGE_STAMP(t, st.steps, 3);
-    if (SAGE_FUSE != 2 && j > 0) mbar_wait(&p_empty[t], ph ^ 1u);
 #else
-    uint32_t w[kFp8 ? 32 : 64];
-    // The exp phases of the two warpgroups alternate (they are the only MUFU-bound stretch): each
-    // warpgroup's load / max / pack / store phases then run under the other one's exponentials.
-    if (kTurn == 1 && j < n_pingpong) named_bar_sync(1 + t, 2 * kTileQ);
-    SAGE_STAMP(t, st.steps, 6);
-    if constexpr (kMask) { /* done above */ }
-    else if (masked_tile) dsum = softmax_exp<true, 0, 128, 3, false>(s, sc, bias, lim);
+    if (masked_tile) dsum = softmax_exp<true, 0, 128, 3, false>(s, sc, bias, lim);
     else dsum = softmax_exp<false, 0, 128, 3, false>(s, sc, bias, 127);
+#endif
+    }
     if (kTurn == 1 && j < n_pingpong) {
       if (t == 0) {
         named_bar_arrive(2, 2 * kTileQ);
@@ -296,65 +332,26 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
     }
     SAGE_STAMP(t, st.steps, 7);
     d_run = fmaf(d_run, alpha, dsum);
-    softmax_pack<kFp8>(s, w);
+    if constexpr (kFuse == 0) softmax_pack<kFp8>(s, w);
     SAGE_STAMP(t, st.steps, 3);
-    // PV(j-1) complete: P tile reusable and O_t stable (at j == 0 the epilogue of the previous item
-    // has already waited for that item's last PV)
-    if (j > 0) mbar_wait(&p_empty[t], ph ^ 1u);
-#endif
-    // P leaves the registers first (w[] is dead after this) ...
-    if (SAGE_FUSE != 2) {
-      if constexpr (kPTmem<D>) {
-        // head_dim 64 leaves 128 TMEM columns free: P_t gets its own columns there (no shared-memory
-        // store, no proxy fence, and the P.V MMA reads A from TMEM instead of the shared-memory port)
-        if constexpr (kFp8) {
-          tmem_st32(tP, *reinterpret_cast<uint32_t(*)[32]>(&w[0]));
-        } else {
-          tmem_st32(tP, *reinterpret_cast<uint32_t(*)[32]>(&w[0]));
-          tmem_st32(tP + 32, *reinterpret_cast<uint32_t(*)[32]>(&w[kFp8 ? 0 : 32]));
-        }
-      } else {
-#pragma unroll
-        for (int c = 0; c < (kFp8 ? 8 : 16); ++c) {
-          const uint32_t addr = prow + (uint32_t)(c >> 3) * (kTileQ * 128) + (((uint32_t)(c & 7) ^ px) << 4);
-          st_shared_v4(addr, w[4 * c], w[4 * c + 1], w[4 * c + 2], w[4 * c + 3]);
-        }
-      }
-    }
-    // ... then O is rescaled when some row of this warp moved its max ...
-    if (j > 0 && __any_sync(0xffffffffu, alpha != 1.0f)) {
-      tc_fence_after();
-#pragma unroll
-      for (int c0 = 0; c0 < D; c0 += 32) {
-        uint32_t o[32];
-        tmem_ld32(tO + c0, o);
-        tc_wait_ld();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
-        tmem_st32(tO + c0, o);
-      }
-    }
-    // ... and the logits of the NEXT step (ready long ago: their MMA went out when this step's S was
-    // drained) start their way into the s[] registers, under the fences and the barrier traffic.
-    const bool s_pref = SAGE_SPREF && (j + 1 < n_iter);
-    if (s_pref) {
-      mbar_wait(&s_full[t], ph ^ 1u);
-      tc_fence_after();
-      load_s();
-    }
-    if constexpr (kPTmem<D>) {
-      tc_wait_st();
+    if constexpr (kPs == 0) rescale_o();
+    // P row -> TMEM, over the S columns just consumed
+    if (kFuse == 2) {
+      // (stored group by group inside the window)
+    } else if constexpr (kPs > 0) {
+      tmem_st_words<kPs * kWg, 8 * kWg>(tS, w);   // (the early part went out inside the window)
+    } else if constexpr (kFp8) {
+      tmem_st32(tS, w);
     } else {
-      tc_wait_st();  // the rescale's stores (no-op otherwise)
-      fence_proxy_async_smem();
+      uint32_t(&w0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&w[0]);
+      uint32_t(&w1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&w[32]);
+      tmem_st32(tS, w0);
+      tmem_st32(tS + 32, w1);
     }
+    tc_wait_st();
     tc_fence_before();
+    if (psplit_groups<D, kFp8>() > 0 && kPs == 0) mbar_arrive(&p_part[t]);   // (attn_mask path: both parts at once)
     mbar_arrive(&p_full[t]);
-    if (s_pref) {
-      tc_wait_ld();
-      tc_fence_before();
-      mbar_arrive(&s_free[t]);
-    }
     SAGE_STAMP(t, st.steps, 4);
     ++st.steps;
   }
@@ -381,11 +378,12 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   uint64_t* v_full = k_empty + kKStages;      // kVStages
   uint64_t* v_empty = v_full + kVStages;      // kVStages
   uint64_t* s_full = v_empty + kVStages;      // 2
-  uint64_t* s_free = s_full + 2;              // 2
-  uint64_t* p_full = s_free + 2;              // 2
-  uint64_t* p_empty = p_full + 2;             // 2
-  uint64_t* o_full = p_empty + 2;             // 2
-  uint64_t* sched_full = o_full + 2;          // kSchedSlots
+  uint64_t* p_full = s_full + 2;              // 2
+  uint64_t* o_full = p_full + 2;              // 2
+  uint64_t* s_free = o_full + 2;              // 2 (SAGE_SSPLIT)
+  uint64_t* p_part = s_free + 2;              // 2 (SAGE_PSPLIT)
+  uint64_t* s_hi = p_part + 2;                // 2 (SAGE_SSPLIT)
+  uint64_t* sched_full = s_hi + 2;            // kSchedSlots
   uint64_t* sched_empty = sched_full + kSchedSlots;
   WorkItem* ring = reinterpret_cast<WorkItem*>(smem + L::kRingOff);
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(smem + L::kTmemPtrOff);
@@ -398,10 +396,11 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     for (int i = 0; i < kVStages; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
     for (int t = 0; t < 2; ++t) {
       mbar_init(&s_full[t], 1);
-      mbar_init(&s_free[t], kTileQ);
       mbar_init(&p_full[t], kTileQ);
-      mbar_init(&p_empty[t], 1);
       mbar_init(&o_full[t], 1);
+      mbar_init(&s_free[t], kTileQ);
+      mbar_init(&p_part[t], kTileQ);
+      mbar_init(&s_hi[t], 1);
     }
     for (int i = 0; i < kSchedSlots; ++i) {
       mbar_init(&sched_full[i], 1);
@@ -440,8 +439,8 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     while (c.valid) {
       float m_run = 0.f, d_run = 1.f;
       if (c.n_iter > 0)
-        softmax_steps<D, kFp8, kMask, kVarlen>(p, t, row, c, ring, it, tmem_base, smem + L::kPOff + t * L::kPBytes,
-                               s_full, s_free, p_full, p_empty, st, m_run, d_run);
+        softmax_steps<D, kFp8, kMask, kVarlen>(p, t, row, c, ring, it, tmem_base, s_full, s_free, p_full, p_part, s_hi, st, m_run,
+                               d_run);
       // the next item is prepared under this item's last P.V
       const bool had_steps = c.n_iter > 0;
       c = softmax_setup<D, kVarlen>(p, t, row, ring, sched_full, it + 1);
@@ -533,16 +532,14 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
       const uint32_t sQ = smem_u32(smem + L::kQOff);
       const uint32_t sK = smem_u32(smem + L::kKOff);
       const uint32_t sV = smem_u32(smem + L::kVOff);
-      const uint32_t sP = smem_u32(smem + L::kPOff);
 
-      uint32_t im = 0, kc = 0, vc = 0;       // items started, K tiles consumed, V tiles consumed
-      uint32_t ns[2] = {0, 0}, np[2] = {0, 0};  // S_t / PV_t issued so far
+      uint32_t im = 0, kc = 0, vc = 0;  // items started, K tiles consumed, V tiles consumed
+      uint32_t np[2] = {0, 0};          // PV_t issued so far
 
-      // S_t = Q_t.K^T of the K tile in ring slot (kc % stages); waits for the warpgroup to have drained
-      // the previous S_t
+      // S_t = Q_t.K^T of the K tile in ring slot (kc % stages).  No "S drained" barrier is needed: the
+      // issuer only gets here after it has issued the P.V that reads P_t (which the warpgroup wrote
+      // after pulling S_t into registers), and the tensor pipe executes in order.
       auto issue_qk = [&](int t, uint32_t qb) {
-        if (ns[t] > 0) mbar_wait(&s_free[t], (ns[t] - 1) & 1u);
-        tc_fence_after();
         const uint32_t a0 = sQ + (qb * 2 + t) * L::kQBytes;
         const uint32_t b0 = sK + (kc % kKStages) * L::kKBytes;
 #pragma unroll
@@ -552,58 +549,47 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
           mma_i8_ss(tmem_base + t * 128, ad, bd, idesc_qk, kk > 0);
         }
         tc_commit(&s_full[t]);
-        ++ns[t];
       };
-#ifdef SAGE_TRACE
-      const bool trace_on = blockIdx.x == 0;
-#endif
+      // SAGE_SSPLIT: the two N = 64 halves of S_t (hi: keys 64..127 -> columns [64, 128); lo: keys 0..63)
+      constexpr uint32_t idesc_qk_half = make_idesc(CFMT_S32, FMT_S8, FMT_S8, 0, 0, kTileQ, kTileKV / 2);
+      uint32_t ns[2] = {0, 0};          // S_t issued so far (whole or split)
+      auto issue_qk_half = [&](int t, uint32_t qb, int hi) {
+        const uint32_t a0 = sQ + (qb * 2 + t) * L::kQBytes;
+        const uint32_t b0 = sK + (kc % kKStages) * L::kKBytes + (hi ? (kTileKV / 2) * D : 0);
+#pragma unroll
+        for (int kk = 0; kk < D / 32; ++kk) {
+          const uint64_t ad = make_smem_desc(a0 + kk * 32, 16, qk_sbo, qk_swz);
+          const uint64_t bd = make_smem_desc(b0 + kk * 32, 16, qk_sbo, qk_swz);
+          mma_i8_ss(tmem_base + t * 128 + (hi ? 64 : 0), ad, bd, idesc_qk_half, kk > 0);
+        }
+      };
       auto issue_pv = [&](int t, bool accumulate) {
-        SAGE_STAMP(2, np[t], t * 4 + 0);
-        mbar_wait(&p_full[t], np[t] & 1u);
-        tc_fence_after();
-        SAGE_STAMP(2, np[t], t * 4 + 1);
-        const uint32_t a0 = sP + t * L::kPBytes;
         const uint32_t b0 = sV + (vc % kVStages) * L::kVBytes;
         const uint32_t d_tmem = tmem_base + 256 + t * D;
-        const uint32_t a_tmem = tmem_base + 384 + t * (kFp8 ? 32 : 64);  // kPTmem only
-        if constexpr (kFp8) {
+        const uint32_t a_tmem = tmem_base + t * 128;
+        constexpr int kSteps = kFp8 ? kTileKV / 32 : kTileKV / 16;
+        constexpr int kPsplit = psplit_groups<D, kFp8>();
+        constexpr int kEarly = kFp8 ? kPsplit / 2 : kPsplit;   // K-steps covered by the early part of P
+        if (kEarly > 0) {
+          mbar_wait(&p_part[t], np[t] & 1u);
+          tc_fence_after();
+        }
 #pragma unroll
-          for (int kk = 0; kk < kTileKV / 32; ++kk) {
-            const uint64_t bd = make_smem_desc(b0 + kk * 32, 16, 1024, SWZ_128B);
-            if constexpr (kPTmem<D>) {
-              mma_f8_ts(d_tmem, a_tmem + kk * 8, bd, idesc_pv, accumulate || (kk > 0));
-            } else {
-              const uint64_t ad = make_smem_desc(a0 + kk * 32, 16, 1024, SWZ_128B);
-              mma_f8_ss(d_tmem, ad, bd, idesc_pv, accumulate || (kk > 0));
-            }
+        for (int kk = 0; kk < kSteps; ++kk) {
+          if (kk == kEarly) {
+            mbar_wait(&p_full[t], np[t] & 1u);
+            tc_fence_after();
           }
-        } else {
-#pragma unroll
-          for (int kk = 0; kk < kTileKV / 16; ++kk) {
+          if constexpr (kFp8) {
+            const uint64_t bd = make_smem_desc(b0 + kk * 32, 16, 1024, SWZ_128B);
+            mma_f8_ts(d_tmem, a_tmem + kk * 8, bd, idesc_pv, accumulate || (kk > 0));
+          } else {
             // MN-major B: 16 kv rows x 128 B per MMA = 2 KB step; 64-wide d blocks 16 KB apart
             const uint64_t bd = make_smem_desc(b0 + kk * 2048, kTileKV * 128, 1024, SWZ_128B);
-            if constexpr (kPTmem<D>) {
-              mma_f16_ts(d_tmem, a_tmem + kk * 8, bd, idesc_pv, accumulate || (kk > 0));
-            } else {
-              // A: two 64-wide K blocks of [128 rows][128 B], 16 KB apart, 32 B per MMA inside a block
-              const uint64_t ad = make_smem_desc(a0 + (kk >> 2) * (kTileQ * 128) + (kk & 3) * 32, 16, 1024, SWZ_128B);
-              mma_f16_ss(d_tmem, ad, bd, idesc_pv, accumulate || (kk > 0));
-            }
+            mma_f16_ts(d_tmem, a_tmem + kk * 8, bd, idesc_pv, accumulate || (kk > 0));
           }
         }
-        tc_commit(&p_empty[t]);
-        SAGE_STAMP(2, np[t], t * 4 + 2);
         ++np[t];
-      };
-      // Q.K^T of kv step `jj` of the item in Q slot `qb` (both tiles), K from the ring
-      auto qk_step = [&](const int (&nit)[2], int jj, uint32_t qb) {
-        mbar_wait(&k_full[kc % kKStages], (kc / kKStages) & 1u);
-#pragma unroll
-        for (int t = 0; t < 2; ++t)
-          if (jj < nit[t]) issue_qk(t, qb);
-        tc_commit(&k_empty[kc % kKStages]);
-        ++kc;
-        if (jj == max(nit[0], nit[1]) - 1) tc_commit(&q_empty[qb]);  // last use of this Q slot
       };
 
       int n_it[2], n_nx[2];
@@ -615,7 +601,24 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         if (have) {
           item_iters_of<kVarlen>(p, w0, n_it);
           mbar_wait(&q_full[0], 0);
-          qk_step(n_it, 0, 0);
+          mbar_wait(&k_full[0], 0);
+          tc_fence_after();
+#pragma unroll
+          for (int t = 0; t < 2; ++t)
+            if (n_it[t] > 0) {
+              if (SAGE_SSPLIT) {
+                issue_qk_half(t, 0, 1);
+                tc_commit(&s_hi[t]);
+                issue_qk_half(t, 0, 0);
+                tc_commit(&s_full[t]);
+              } else {
+                issue_qk(t, 0);
+              }
+              ++ns[t];
+            }
+          tc_commit(&k_empty[0]);
+          ++kc;
+          if (max(n_it[0], n_it[1]) == 1) tc_commit(&q_empty[0]);
         }
       }
       while (have) {
@@ -626,25 +629,48 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         const int n_max = max(n_it[0], n_it[1]);
         const uint32_t qb = im % kQStages;
         for (int j = 0; j < n_max; ++j) {
-          // the next Q.K^T (of this item, or the first one of the next item) goes out before the
-          // issuer blocks on this step's P tiles
-          if (j + 1 < n_max) {
-            qk_step(n_it, j + 1, qb);
-          } else if (have_nxt) {
-            const uint32_t qn = (im + 1) % kQStages;
-            mbar_wait(&q_full[qn], ((im + 1) / kQStages) & 1u);
-            qk_step(n_nx, 0, qn);
-          }
           mbar_wait(&v_full[vc % kVStages], (vc / kVStages) & 1u);
+          // what follows P_t.V(j) on the tensor pipe: S_t(j+1) of this item, or S_t(0) of the next
+          const bool more = (j + 1 < n_max);
+          const bool cross = !more && have_nxt;
+          const int jn = more ? j + 1 : 0;
+          const int nn0 = more ? n_it[0] : n_nx[0], nn1 = more ? n_it[1] : n_nx[1];
+          const uint32_t qn = more ? qb : (im + 1) % kQStages;
+          if (more || cross) {
+            if (cross) mbar_wait(&q_full[qn], ((im + 1) / kQStages) & 1u);
+            mbar_wait(&k_full[kc % kKStages], (kc / kKStages) & 1u);
+            tc_fence_after();
+          }
 #pragma unroll
           for (int t = 0; t < 2; ++t) {
+            if (SAGE_SSPLIT && (more || cross) && jn < (t == 0 ? nn0 : nn1)) {
+              // upper half of the next S_t first: it only needs the warpgroup to have drained the current one
+              if (ns[t] > 0) mbar_wait(&s_free[t], (ns[t] - 1) & 1u);
+              tc_fence_after();
+              issue_qk_half(t, qn, 1);
+              tc_commit(&s_hi[t]);
+            }
             if (j < n_it[t]) {
               issue_pv(t, j > 0);
               if (j == n_it[t] - 1) tc_commit(&o_full[t]);
             }
+            if (t == 1) tc_commit(&v_empty[vc % kVStages]);
+            if ((more || cross) && jn < (t == 0 ? nn0 : nn1)) {
+              if (SAGE_SSPLIT) {
+                issue_qk_half(t, qn, 0);
+                tc_commit(&s_full[t]);
+              } else {
+                issue_qk(t, qn);
+              }
+              ++ns[t];
+            }
           }
-          tc_commit(&v_empty[vc % kVStages]);
           ++vc;
+          if (more || cross) {
+            tc_commit(&k_empty[kc % kKStages]);
+            ++kc;
+            if (jn == max(nn0, nn1) - 1) tc_commit(&q_empty[qn]);  // last use of that Q slot
+          }
         }
         ++im;
         n_it[0] = n_nx[0];
@@ -664,12 +690,13 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   }
 }
 
-}  // namespace sage
+}  // namespace sage_attn
 
 // ==========================================================================================
 // Host side: TMA descriptors + launch
 // ==========================================================================================
-namespace sage {
+namespace sage_attn {
+using namespace sage;
 
 template <int D, bool kFp8, bool kMask = false, bool kVarlen = false>
 static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
@@ -758,29 +785,5 @@ static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
   return 0;
 }
 
-}  // namespace sage
+}  // namespace sage_attn
 
-// head_dim 64 with f16 P also runs on this kernel (P in spare TMEM columns, S(j+1) issued as soon as
-// S(j) is drained); called from sage_attn_i8_f16 in attn_f16_sm100.cu
-namespace sage {
-int launch_attn_f16_d64(const sage_attn_args* a, cudaStream_t stream) {
-  if (a->cu_seqlens_q != nullptr) return launch_attn<64, false, false, true>(a, stream);
-  return a->mask ? launch_attn<64, false, true>(a, stream) : launch_attn<64, false>(a, stream);
-}
-}  // namespace sage
-
-#ifdef SAGE_TRACE
-extern "C" int sage_debug_trace(long long* out) {
-  return (int)cudaMemcpyFromSymbol(out, sage::g_trace, sizeof(sage::g_trace));
-}
-#endif
-
-extern "C" int sage_attn_i8_f8(const sage_attn_args* a, void* stream) {
-  int rc = sage::check_attn_args(a);
-  if (rc) return rc;
-  SAGE_REQUIRE(a->cu_seqlens_q == nullptr, "varlen is an f16-P.V path (sage_attn_i8_f16)");
-  cudaStream_t s = reinterpret_cast<cudaStream_t>(stream);
-  if (a->mask != nullptr)
-    return a->D == 128 ? sage::launch_attn<128, true, true>(a, s) : sage::launch_attn<64, true, true>(a, s);
-  return a->D == 128 ? sage::launch_attn<128, true>(a, s) : sage::launch_attn<64, true>(a, s);
-}

@@ -1,4 +1,4 @@
-// Per-row softmax arithmetic of the sm_100a attention kernel (shared by attn_sm100.cu and the
+// Per-row softmax arithmetic of the sm_100a attention kernel (shared by attn_kernel_sm100.cuh and the
 // stand-alone softmax microbenchmark tools/softmax_bench.cu).
 #pragma once
 #include <cstdint>
@@ -111,6 +111,34 @@ __device__ __forceinline__ void softmax_max_tree(const uint32_t (&s)[128], const
   for (int k = 0; k < 8; ++k) cand[k] = (float)mx[k] * sc[k];
   const float mrow = fmaxf(fmaxf(fmaxf(cand[0], cand[1]), fmaxf(cand[2], cand[3])),
                            fmaxf(fmaxf(cand[4], cand[5]), fmaxf(cand[6], cand[7])));
+  const bool grow = mrow > m_run + (kFp8 ? kFp8Tau : kF16Tau);
+  float m_new = m_run;
+  alpha = 1.0f;
+  if (__any_sync(0xffffffffu, grow)) {
+    m_new = fmaxf(m_run, mrow);
+    alpha = ex2_approx(m_run - m_new);
+  }
+  m_run = m_new;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) bias[k] = fmaf(-kMagicF, sc[k], (kFp8 ? kFp8Offset : 0.f) - m_new);
+}
+
+// softmax_max<kFp8, false> in two halves (unmasked tiles): the integer class maxima of columns [64 * kHalf, 64 * kHalf + 64)
+// (classes 4 * kHalf .. 4 * kHalf + 3) can be taken as soon as that half of S is in registers; softmax_max_finish then
+// gives exactly what softmax_max gives (integer and float maxima do not depend on the order).
+template <int kHalf>
+__device__ __forceinline__ void softmax_halfmax(const uint32_t (&s)[128], int (&mx)[8]) {
+#pragma unroll
+  for (int k = 4 * kHalf; k < 4 * kHalf + 4; ++k) mx[k] = kMaskedS;
+#pragma unroll
+  for (int c = 64 * kHalf; c < 64 * kHalf + 64; ++c) mx[kcls(c)] = max(mx[kcls(c)], (int)s[c]);
+}
+template <bool kFp8>
+__device__ __forceinline__ void softmax_max_finish(const int (&mx)[8], const float (&sc)[8], float& m_run, float& alpha,
+                                                   float (&bias)[8]) {
+  float mrow = -1e30f;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) mrow = fmaxf(mrow, (float)mx[k] * sc[k]);
   const bool grow = mrow > m_run + (kFp8 ? kFp8Tau : kF16Tau);
   float m_new = m_run;
   alpha = 1.0f;

@@ -16,7 +16,7 @@ finally:
     os.remove(tmp)
 # the variant replaces the unit(s) whose entry points it defines (older experiments define both)
 text = open(src).read()
-drop = {"attn_sm100.cu"} if 'int sage_attn_i8_f8(' in text else set()
+drop = {"attn_f8_sm100.cu"} if 'int sage_attn_i8_f8(' in text else set()
 if 'int sage_attn_i8_f16(' in text:
     drop.add("attn_f16_sm100.cu")
 objs = [os.path.join(B.OBJ, n + ".o") for n, _ in B.UNITS if n not in drop] + [obj]

@@ -59,14 +59,16 @@ for name in names:
     else:
         worst = 1.0
         dl = 0.0
+        do = 0.0
         for key, (o, lse) in cur.items():
             ro, rl = ref[key]
+            do = max(do, (o.float() - ro.float()).abs().max().item())
             cos = torch.nn.functional.cosine_similarity(o.float().flatten(), ro.float().flatten(), dim=0).item()
             worst = min(worst, cos)
             dl = max(dl, (lse - rl).abs().max().item())
             if not torch.isfinite(o.float()).all():
                 worst = float("nan")
-        print(f"[{name}] vs {names[0]}: worst cos {worst:.7f}  max |dLSE| {dl:.2e}", flush=True)
+        print(f"[{name}] vs {names[0]}: worst cos {worst:.7f}  max |dO| {do:.2e}  max |dLSE| {dl:.2e}", flush=True)
     tmp = os.path.join(ROOT, "gpurun_out", f"_sweep_{name}.jsonl")
     if os.path.exists(tmp):
         os.remove(tmp)

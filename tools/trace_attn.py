@@ -1,5 +1,5 @@
 """Pipeline timeline of CTA 0 of the attention kernel across its first work items (development tool).
-    python tools/build_variant.py trace sageattention_b200/csrc/attn_sm100.cu -DSAGE_TRACE
+    python tools/build_flags.py trace --only attn_f16_sm100.cu -DSAGE_TRACE     (attn_f8_sm100.cu for the e4m3 flavour)
     SAGE_B200_LIB=tools/_bin/libsage_trace.so python tools/trace_attn.py [f8|f16] [head_dim] [N] [causal]
 Prints, per KV step (counted across items), SM-clock intervals of the two softmax warpgroups."""
 import ctypes, os, sys
