@@ -83,6 +83,22 @@ using namespace sage;
 #define SAGE_PSPLIT_LAG 0
 #endif
 
+// 1: the step works through S in two halves, UPPER half first (softmax_steps_spec below): its exponentials are computed
+// against the running maximum the row already has - which is what the lazily rescaled softmax would use anyway unless
+// the row's maximum grows by more than tau in this tile - while the tensor pipe is still busy with P.V(j-1) (late part)
+// and the lower half of Q.K^T(j).  When the lower half is in, the step decides as before; in the rare step where a row of
+// the warp does grow, the upper half is pulled from TMEM again (it is still there: s_free is only signalled after the
+// decision) and redone.  P then goes out as [upper half | lower half], and P.V(j) is issued in that order of K-steps.
+#ifndef SAGE_SPEC
+#define SAGE_SPEC 0
+#endif
+// 2: one MMA issuer warp per Q tile (warps 9 and 10) instead of one for both.  A single in-order issuer serves the
+// barriers of warpgroup 0 and warpgroup 1 alternately, so a P part of one warpgroup that is ready waits while the issuer
+// is blocked on the other warpgroup's next barrier; with two issuers each warpgroup's MMAs go out as soon as its own
+// barriers allow.  The K / V / Q ring slots are then released by two commits (one per issuer).
+#ifndef SAGE_ISSUERS
+#define SAGE_ISSUERS 1
+#endif
 #ifndef SAGE_PSPLIT_SMALL
 #define SAGE_PSPLIT_SMALL 4   // the e4m3 flavour and head_dim 64 (shorter P.V): measured best at 4
 #endif
@@ -360,6 +376,228 @@ __device__ __forceinline__ void softmax_steps(const AttnKernelParams& p, int t, 
   d_out = d_run;
 }
 
+// The 8 class scales of kv tile j (log2e * sm_scale * q_scale * k_scale[class]).
+template <bool kVarlen>
+__device__ __forceinline__ void load_class_scales(const AttnKernelParams& p, const ItemCtx& c, int j, float qs,
+                                                  float (&sc)[8]) {
+  const float* ksp = c.ksp;
+  if constexpr (!kVarlen) {
+    if (p.gran == 3) {
+      // per_thread: 8 consecutive floats (2 blocks of 64 rows x 4 groups).  A second block beyond kv_len (ragged last
+      // tile) has no scales: all its columns are masked, any finite factor will do - the first block's are reused
+      const float4 s0 = __ldg(reinterpret_cast<const float4*>(ksp + j * 8));
+      const float4 s1 = (j * 8 + 4 < p.k_scale_per_bh) ? __ldg(reinterpret_cast<const float4*>(ksp + j * 8 + 4)) : s0;
+      sc[0] = s0.x * qs; sc[1] = s0.y * qs; sc[2] = s0.z * qs; sc[3] = s0.w * qs;
+      sc[4] = s1.x * qs; sc[5] = s1.y * qs; sc[6] = s1.z * qs; sc[7] = s1.w * qs;
+    } else {
+      // per_warp / per_block: one scale per 64 kv rows
+      const float a0 = __ldg(ksp + min(j * 2, p.k_scale_per_bh - 1)) * qs;
+      const float a1 = __ldg(ksp + min(j * 2 + 1, p.k_scale_per_bh - 1)) * qs;
+      sc[0] = sc[1] = sc[2] = sc[3] = a0;
+      sc[4] = sc[5] = sc[6] = sc[7] = a1;
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      int idx = j * 2 + (k >> 2);             // per-block scales of the sequence, [blocks, H]
+      idx = max(min(idx, c.ks_count - 1), 0);   // (0 blocks: the key-less sequence's one masked step)
+      sc[k] = __ldg(ksp + (size_t)idx * c.ks_stride) * qs;
+    }
+  }
+}
+
+// The kv steps of one work item for Q tile `t`, upper half of S first and speculatively (SAGE_SPEC, see the top).
+template <int D, bool kFp8, bool kMask, bool kVarlen = false>
+__device__ __forceinline__ void softmax_steps_spec(const AttnKernelParams& p, int t, int row,
+                                                   const ItemCtx& c, const WorkItem* ring, uint32_t it,
+                                                   uint32_t tmem_base, uint64_t* s_full, uint64_t* s_free, uint64_t* p_full,
+                                                   uint64_t* p_part, uint64_t* s_hi, WgState& st, float& m_out, float& d_out) {
+  const int warp_in_wg = (row >> 5);
+  const uint32_t lane_off = (uint32_t)(warp_in_wg * 32) << 16;
+  const uint32_t tS = tmem_base + lane_off + (uint32_t)(t * 128);
+  const uint32_t tO = tmem_base + lane_off + (uint32_t)(256 + t * D);
+  const int q_row = c.q_row;
+  const float qs = c.qs * p.sm_scale_log2;  // folded with sm_scale * log2 e
+  const int n_iter = c.n_iter;
+  constexpr int kWg = kFp8 ? 4 : 8;          // packed words per 16-column group
+  constexpr float kTau = kFp8 ? kFp8Tau : kF16Tau;
+  constexpr float kOff = kFp8 ? kFp8Offset : 0.f;
+  float m_run = -1e30f, d_run = 0.f;
+#ifdef SAGE_TRACE
+  const bool trace_on = blockIdx.x == 0 && row == 0;
+#endif
+
+  for (int j = 0; j < n_iter; ++j) {
+    const uint32_t ph = st.steps & 1u;
+    float sc[8];
+    load_class_scales<kVarlen>(p, c, j, qs, sc);
+    const int kv0 = j * kTileKV;
+    const int k_len = kVarlen ? c.k_len : p.Nk;
+    int lim = k_len - 1 - kv0;
+    if (p.causal) lim = min(lim, q_row - kv0);
+    const bool masked_tile = (j == n_iter - 1) && (p.causal || (k_len - kv0) < kTileKV);
+    SAGE_STAMP(t, st.steps, 0);
+    uint32_t s[128];
+    uint32_t w[kFp8 ? 32 : 64];
+    uint32_t(&s0)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[0]);
+    uint32_t(&s1)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[32]);
+    uint32_t(&s2)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[64]);
+    uint32_t(&s3)[32] = *reinterpret_cast<uint32_t(*)[32]>(&s[96]);
+    float alpha = 1.0f, bias[8], dsum;
+    uint64_t dsum2 = 0;
+
+    auto load_hi = [&]() {
+      tmem_ld32(tS + 64, s2);
+      tmem_ld32(tS + 96, s3);
+      tc_wait_ld();
+    };
+    auto wait_load_lo = [&]() {
+      mbar_wait(&s_full[t], ph);
+      tc_fence_after();
+      SAGE_STAMP(t, st.steps, 1);
+      tmem_ld32(tS + 0, s0);
+      tmem_ld32(tS + 32, s1);
+      tc_wait_ld();
+      SAGE_STAMP(t, st.steps, 2);
+    };
+    auto release_s_hi = [&]() {   // the upper 64 columns of S_t are no longer needed (P only uses the lower 64)
+      tc_fence_before();
+      mbar_arrive(&s_free[t]);
+    };
+    auto debug_dump = [&]() {
+      if (p.debug_s != nullptr && j == 0) {
+        const int nq_pad = (p.Nq + 255) / 256 * 256;
+        const int4 wv = ld_shared_v4(smem_u32(&ring[it % kSchedSlots]));
+        WorkItem wi; wi.h = wv.y; wi.b = wv.z;
+        int* dst = p.debug_s + ((size_t)(wi.b * p.Hq + wi.h) * nq_pad + q_row) * 128;
+#pragma unroll
+        for (int cc = 0; cc < 128; ++cc) dst[cc] = (int)s[cc];
+      }
+    };
+    // exponentials + conversions of one half (4 groups of 16 columns) into its words of w
+    auto exp_half = [&](auto half_c, auto masked_c) {
+      constexpr int kH = decltype(half_c)::value;
+      constexpr bool kM = decltype(masked_c)::value;
+#pragma unroll
+      for (int g = 4 * kH; g < 4 * kH + 4; ++g) {
+        uint32_t(&wg)[kWg] = *reinterpret_cast<uint32_t(*)[kWg]>(&w[g * kWg]);
+        softmax_exp_pack16<kFp8, kM>(g, s, sc, bias, kM ? lim : 127, dsum2, wg);
+      }
+    };
+    auto set_bias = [&]() {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) bias[k] = fmaf(-kMagicF, sc[k], kOff - m_run);
+    };
+    // rescale O when some row of this warp moved its max (PV(j-1) is complete: the lower half of S(j) was issued after
+    // it and tcgen05.commit tracks all earlier MMAs) - before any part of P.V(j) may start
+    auto rescale_o = [&]() {
+      if (j > 0) {
+        if (__any_sync(0xffffffffu, alpha != 1.0f)) {
+#pragma unroll
+          for (int c0 = 0; c0 < D; c0 += 32) {
+            uint32_t o[32];
+            tmem_ld32(tO + c0, o);
+            tc_wait_ld();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) o[i] = __float_as_uint(__uint_as_float(o[i]) * alpha);
+            tmem_st32(tO + c0, o);
+          }
+        }
+      }
+    };
+    auto publish_hi = [&]() {   // P of keys 64..127 -> the upper half of the P columns; P.V(j) may start on them
+      tmem_st_words<4 * kWg, 8 * kWg>(tS, w);
+      tc_wait_st();
+      tc_fence_before();
+      mbar_arrive(&p_part[t]);
+    };
+    auto publish_lo = [&]() {
+      tmem_st_words<0, 4 * kWg>(tS, w);
+      tc_wait_st();
+      tc_fence_before();
+      mbar_arrive(&p_full[t]);
+    };
+
+    mbar_wait(&s_hi[t], ph);
+    tc_fence_after();
+    load_hi();
+    if constexpr (kMask) {
+      wait_load_lo();
+      release_s_hi();
+      debug_dump();
+      // attn_mask: max, exponentials and row sum of y = logit + mask in one call (softmax_sm100.cuh)
+      dsum = softmax_general_mask<kFp8>(s, sc, lim, c.mask_row + (size_t)kv0 * (p.mask_kind == 1 ? 1 : 2), p.mask_kind,
+                                        m_run, alpha);
+      softmax_pack<kFp8>(s, w);
+      SAGE_STAMP(t, st.steps, 5);
+      rescale_o();
+      publish_hi();
+      SAGE_STAMP(t, st.steps, 7);
+      publish_lo();
+    } else if (masked_tile) {
+      wait_load_lo();
+      release_s_hi();
+      debug_dump();
+      softmax_max<kFp8, true, false>(s, sc, lim, m_run, alpha, bias);
+      rescale_o();
+      exp_half(std::integral_constant<int, 1>{}, std::true_type{});
+      publish_hi();
+      SAGE_STAMP(t, st.steps, 5);
+      exp_half(std::integral_constant<int, 0>{}, std::true_type{});
+      SAGE_STAMP(t, st.steps, 7);
+      publish_lo();
+      float d0, d1;
+      unpack2(dsum2, d0, d1);
+      dsum = d0 + d1;
+    } else {
+      int mx[8];
+      softmax_halfmax<1>(s, mx);
+      float cand = -1e30f;
+#pragma unroll
+      for (int k = 4; k < 8; ++k) cand = fmaxf(cand, (float)mx[k] * sc[k]);
+      // no row of the warp can grow beyond tau because of its upper half: start on it with the maximum it has
+      const bool spec = !__any_sync(0xffffffffu, cand > m_run + kTau);
+      set_bias();
+      if (spec) exp_half(std::integral_constant<int, 1>{}, std::false_type{});
+      SAGE_STAMP(t, st.steps, 6);
+      wait_load_lo();
+      debug_dump();
+      softmax_halfmax<0>(s, mx);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) cand = fmaxf(cand, (float)mx[k] * sc[k]);
+      if (__any_sync(0xffffffffu, cand > m_run + kTau)) {
+        const float m_new = fmaxf(m_run, cand);
+        alpha = ex2_approx(m_run - m_new);  // 0 on the first tile (m_run = -1e30)
+        m_run = m_new;
+        set_bias();
+        if (spec) {   // rare: the upper half was done against the old maximum - fetch it again and redo it
+          load_hi();
+          dsum2 = 0;
+        }
+        release_s_hi();
+        exp_half(std::integral_constant<int, 1>{}, std::false_type{});
+      } else {
+        release_s_hi();
+      }
+      rescale_o();
+      publish_hi();
+      SAGE_STAMP(t, st.steps, 5);
+      exp_half(std::integral_constant<int, 0>{}, std::false_type{});
+      SAGE_STAMP(t, st.steps, 7);
+      publish_lo();
+      float d0, d1;
+      unpack2(dsum2, d0, d1);
+      dsum = d0 + d1;
+    }
+    d_run = fmaf(d_run, alpha, dsum);
+    SAGE_STAMP(t, st.steps, 3);
+    SAGE_STAMP(t, st.steps, 4);
+    ++st.steps;
+  }
+  m_out = m_run;
+  d_out = d_run;
+}
+
 // ------------------------------------------------------------------------------------------
 template <int D, bool kFp8, bool kMask = false, bool kVarlen = false>
 __global__ void __launch_bounds__(kThreads, 1)
@@ -391,9 +629,9 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
   const int warp = threadIdx.x >> 5;
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < kQStages; ++i) { mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], 1); }
-    for (int i = 0; i < kKStages; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], 1); }
-    for (int i = 0; i < kVStages; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], 1); }
+    for (int i = 0; i < kQStages; ++i) { mbar_init(&q_full[i], 1); mbar_init(&q_empty[i], SAGE_ISSUERS); }
+    for (int i = 0; i < kKStages; ++i) { mbar_init(&k_full[i], 1); mbar_init(&k_empty[i], SAGE_ISSUERS); }
+    for (int i = 0; i < kVStages; ++i) { mbar_init(&v_full[i], 1); mbar_init(&v_empty[i], SAGE_ISSUERS); }
     for (int t = 0; t < 2; ++t) {
       mbar_init(&s_full[t], 1);
       mbar_init(&p_full[t], kTileQ);
@@ -404,7 +642,7 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     }
     for (int i = 0; i < kSchedSlots; ++i) {
       mbar_init(&sched_full[i], 1);
-      mbar_init(&sched_empty[i], kSoftmaxThreads + 1);  // every softmax thread + the MMA issuer
+      mbar_init(&sched_empty[i], kSoftmaxThreads + SAGE_ISSUERS);  // every softmax thread + the MMA issuer(s)
     }
     fence_barrier_init();
   }
@@ -439,8 +677,13 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
     while (c.valid) {
       float m_run = 0.f, d_run = 1.f;
       if (c.n_iter > 0)
+#if SAGE_SPEC
+        softmax_steps_spec<D, kFp8, kMask, kVarlen>(p, t, row, c, ring, it, tmem_base, s_full, s_free, p_full, p_part, s_hi,
+                                                    st, m_run, d_run);
+#else
         softmax_steps<D, kFp8, kMask, kVarlen>(p, t, row, c, ring, it, tmem_base, s_full, s_free, p_full, p_part, s_hi, st, m_run,
                                d_run);
+#endif
       // the next item is prepared under this item's last P.V
       const bool had_steps = c.n_iter > 0;
       c = softmax_setup<D, kVarlen>(p, t, row, ring, sched_full, it + 1);
@@ -518,9 +761,11 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         cur = nxt;
       }
     }
-  } else if (warp == 9) {
-    // ======================= MMA issuer =======================
+  } else if (warp == 9 || (SAGE_ISSUERS == 2 && warp == 10)) {
+    // ======================= MMA issuer(s) =======================
     reg_dealloc<kIssueRegs>();
+    // the Q tiles this warp issues for: both, or one each
+    const int t_lo = (SAGE_ISSUERS == 2) ? warp - 9 : 0, t_hi = (SAGE_ISSUERS == 2) ? warp - 8 : 2;
     if (elect_one()) {
       constexpr uint32_t idesc_qk = make_idesc(CFMT_S32, FMT_S8, FMT_S8, 0, 0, kTileQ, kTileKV);
       constexpr uint32_t idesc_pv =
@@ -568,25 +813,28 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
         const uint32_t d_tmem = tmem_base + 256 + t * D;
         const uint32_t a_tmem = tmem_base + t * 128;
         constexpr int kSteps = kFp8 ? kTileKV / 32 : kTileKV / 16;
-        constexpr int kPsplit = psplit_groups<D, kFp8>();
+        constexpr int kPsplit = SAGE_SPEC ? 4 : psplit_groups<D, kFp8>();
         constexpr int kEarly = kFp8 ? kPsplit / 2 : kPsplit;   // K-steps covered by the early part of P
         if (kEarly > 0) {
           mbar_wait(&p_part[t], np[t] & 1u);
           tc_fence_after();
         }
 #pragma unroll
-        for (int kk = 0; kk < kSteps; ++kk) {
-          if (kk == kEarly) {
+        for (int ki = 0; ki < kSteps; ++ki) {
+          if (ki == kEarly) {
             mbar_wait(&p_full[t], np[t] & 1u);
             tc_fence_after();
           }
+          // SAGE_SPEC: the early part of P is the UPPER half of the keys
+          const int kk = SAGE_SPEC ? (ki + kSteps / 2) % kSteps : ki;
+          const bool acc = accumulate || (ki > 0);
           if constexpr (kFp8) {
             const uint64_t bd = make_smem_desc(b0 + kk * 32, 16, 1024, SWZ_128B);
-            mma_f8_ts(d_tmem, a_tmem + kk * 8, bd, idesc_pv, accumulate || (kk > 0));
+            mma_f8_ts(d_tmem, a_tmem + kk * 8, bd, idesc_pv, acc);
           } else {
             // MN-major B: 16 kv rows x 128 B per MMA = 2 KB step; 64-wide d blocks 16 KB apart
             const uint64_t bd = make_smem_desc(b0 + kk * 2048, kTileKV * 128, 1024, SWZ_128B);
-            mma_f16_ts(d_tmem, a_tmem + kk * 8, bd, idesc_pv, accumulate || (kk > 0));
+            mma_f16_ts(d_tmem, a_tmem + kk * 8, bd, idesc_pv, acc);
           }
         }
         ++np[t];
@@ -603,8 +851,7 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
           mbar_wait(&q_full[0], 0);
           mbar_wait(&k_full[0], 0);
           tc_fence_after();
-#pragma unroll
-          for (int t = 0; t < 2; ++t)
+          for (int t = t_lo; t < t_hi; ++t)
             if (n_it[t] > 0) {
               if (SAGE_SSPLIT) {
                 issue_qk_half(t, 0, 1);
@@ -641,8 +888,7 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
             mbar_wait(&k_full[kc % kKStages], (kc / kKStages) & 1u);
             tc_fence_after();
           }
-#pragma unroll
-          for (int t = 0; t < 2; ++t) {
+          for (int t = t_lo; t < t_hi; ++t) {
             if (SAGE_SSPLIT && (more || cross) && jn < (t == 0 ? nn0 : nn1)) {
               // upper half of the next S_t first: it only needs the warpgroup to have drained the current one
               if (ns[t] > 0) mbar_wait(&s_free[t], (ns[t] - 1) & 1u);
@@ -654,7 +900,7 @@ sage_attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_const
               issue_pv(t, j > 0);
               if (j == n_it[t] - 1) tc_commit(&o_full[t]);
             }
-            if (t == 1) tc_commit(&v_empty[vc % kVStages]);
+            if (t == t_hi - 1) tc_commit(&v_empty[vc % kVStages]);
             if ((more || cross) && jn < (t == 0 ? nn0 : nn1)) {
               if (SAGE_SSPLIT) {
                 issue_qk_half(t, qn, 0);

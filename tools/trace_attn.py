@@ -29,9 +29,14 @@ t = np.frombuffer(buf, dtype=np.int64).reshape(3, steps, slots).copy()
 t0 = t[0, 0, 0]
 t -= t0
 print(f"{kind} D={D} N={N} causal={causal}")
+spec = bool(int(os.environ.get("TRACE_SPEC", "0")))   # stamps of softmax_steps_spec (SAGE_SPEC)
 for j in range(0, 40):
     for g in range(2):
         a = t[g, j]
+        if spec:
+            print(f"j={j:2d} WG{g}: start {a[0]:7d} upper half (ld, max, exp) {a[6]-a[0]:5d} idle for lower S {a[1]-a[6]:5d} ld {a[2]-a[1]:4d} "
+                  f"max + decision + publish upper {a[5]-a[2]:5d} exp lower {a[7]-a[5]:5d} publish lower {a[4]-a[7]:4d} | period {t[g, j+1, 0]-a[0]:5d}")
+            continue
         ep = f" | setup {a[10]-a[4]:5d} PVwait {a[8]-a[10]:5d} bar {a[11]-a[8]:5d} epilogue {a[9]-a[11]:5d}" if a[9] > 0 else ""
         m = t[2, j]
         ep += f" | MMA: wait_begin {m[g*4]-a[4]:6d} P_seen {m[g*4+1]-a[4]:5d} pv_issued {m[g*4+2]-a[4]:5d} (rel. to P arrive)"
