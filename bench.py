@@ -324,6 +324,26 @@ def run_sp(dev, world, rank, barrier, max_over_ranks, transport="nccl", chunks=1
                 "ms": round(ms, 3), "tops": round(flops / (ms * 1e-3) * 1e-12, 1), "comm_ms": round(comm_ms, 3),
                 "efficiency": round(one_ms / (world * ms), 4),
                 "a2a_bytes_per_rank": int(4 * b * n_loc * h * d * 2 * (world - 1) / world)})
+    # the same layer with the quantised payload: pre-pass on the sequence shards, INT8 / e4m3 codes and
+    # scales through the inbound all-to-alls (1 byte per element instead of 2), 16-bit output back
+    try:
+        class _NullAttention(parallel._Q8CudaOps):
+            def attention(self, q8, k8, v8, q_scale, k_scale, v_scale, out_dtype, is_causal, sm_scale):
+                return torch.empty((1, q8.size(1), q8.size(2), q8.size(3)), dtype=out_dtype, device=q8.device)
+        full8 = lambda: parallel.ulysses_sageattn(qs, ks_, vs_, payload="int8", is_causal=False)
+        comm8 = lambda: parallel.ulysses_sageattn(qs, ks_, vs_, payload="int8", _q8_ops=_NullAttention(), is_causal=False)
+        ms8 = timed(full8)
+        comm8_ms = timed(comm8)
+        m_rows = (n_loc + 127) // 128 * 128
+        rec["int8_payload"] = {
+            "ms": round(ms8, 3), "tops": round(flops / (ms8 * 1e-3) * 1e-12, 1),
+            "comm_and_prepass_ms": round(comm8_ms, 3), "efficiency": round(one_ms / (world * ms8), 4),
+            "a2a_bytes_per_rank": int((3 * m_rows + 2 * n_loc) * b * h * d * (world - 1) / world),
+            "note": "comm_and_prepass_ms = the call with a null attention kernel: statistics, halo exchange, quantisers, "
+                    "both inbound all-to-alls, re-assembly, outbound all-to-all (the 16-bit path's comm_ms excludes its "
+                    "pre-pass, which runs inside the attention call there)"}
+    except Exception as e:  # the record of the default path must survive a failure here
+        rec["int8_payload"] = {"error": f"{type(e).__name__}: {e}"[:300]}
     return rec
 
 

@@ -173,6 +173,22 @@ int sage_per_channel_fp8_flat(sage_tensor4 v, uint8_t* v_out, int64_t vo_stride_
                               int64_t vo_stride_d, float* v_scale, int B, int H, int N, int n_stat, int D, int dtype,
                               float scale_max, void* workspace, void* stream);
 
+/* Sequence-parallel callers that quantise BEFORE the all-to-all (the reference's only sequence-parallel
+ * precedent is the xDiT monkey patch of /root/reference/example/parallel_sageattn_cogvideo.py:43-52, which ships the
+ * 16-bit activations): the partial statistics of this rank's sequence shard x [B,H,N,D] - raw f32 column sums
+ * (sum_out [B,H,D], for the global mean of K: the caller adds the ranks' sums, multiplies by 1/N_total and rounds to the
+ * input dtype, which is sage_seq_mean's arithmetic) and max|x| per channel (absmax_out [B,H,D], for the global range of V:
+ * the caller takes the maximum over ranks).  Either output may be NULL.  Workspace: sage_seq_mean_workspace_bytes(). */
+int sage_col_sum_absmax(sage_tensor4 x, float* sum_out, float* absmax_out, int B, int H, int N, int D, int dtype,
+                        void* workspace, void* stream);
+/* The conversion half of sage_per_channel_fp8_flat for a channel range the CALLER provides (absmax [B,H,D] f32 = max|v|
+ * over the whole sequence, of which v may be one shard): e4m3 codes in the reference's [B,H,D,Npad] layout with its
+ * 16-token permutation (/root/reference/csrc/fused/fused.cu:262-427); v_scale_out (or NULL) receives absmax / scale_max.
+ * With the full sequence's range the codes and scales are bit-identical to sage_per_channel_fp8's. */
+int sage_v_fp8_from_absmax(sage_tensor4 v, uint8_t* v_out, int64_t vo_stride_b, int64_t vo_stride_h, int64_t vo_stride_d,
+                           const float* absmax, float* v_scale_out, int B, int H, int N, int n_stat, int D, int dtype,
+                           float scale_max, void* stream);
+
 /* Attention kernels.  q8/k8: int8 [B,H,N,D] via strides; scales laid out exactly as the reference
  * quantizers produce them; o: f16/bf16 via strides; lse: [B,Hq,Nq] fp32 or NULL (base-2, as the
  * reference kernels return it). */

@@ -72,6 +72,9 @@ SIGNATURES = {
                                      c_int, c_int, c_int, c_f32, c_int, c_vp, c_vp]),
     "sage_per_channel_fp8_flat": (c_int, [Tensor4, c_vp, c_i64, c_i64, c_i64, c_vp, c_int, c_int, c_int, c_int, c_int, c_int,
                                           c_f32, c_vp, c_vp]),
+    "sage_col_sum_absmax": (c_int, [Tensor4, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp]),
+    "sage_v_fp8_from_absmax": (c_int, [Tensor4, c_vp, c_i64, c_i64, c_i64, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int,
+                                       c_int, c_f32, c_vp]),
     "sage_attn_i8_f16": (c_int, [ctypes.POINTER(AttnArgs), c_vp]),
     "sage_attn_i8_f8": (c_int, [ctypes.POINTER(AttnArgs), c_vp]),
     "sage_sageattn_fwd_workspace_bytes": (ctypes.c_size_t, [ctypes.POINTER(FwdArgs)]),
@@ -88,7 +91,7 @@ KERNELS_PER_CALL = {
     # smooth_v: statistics + conversion; otherwise one cluster launch
     "sage_per_channel_fp8": (lambda a: 2 if a[14] else 1),
     "sage_attn_i8_f16": 1, "sage_attn_i8_f8": 1,
-    "sage_per_channel_fp8_flat": 2,
+    "sage_per_channel_fp8_flat": 2, "sage_col_sum_absmax": 1, "sage_v_fp8_from_absmax": 1,
     # prologue + attention; above 65 536 kv rows the prologue is flat launches (K mean, Q, K, V range, V conversion /
     # f16 copy of a bf16 V)
     "sage_sageattn_fwd": (lambda a: 2 if a[0].Nk <= 65536 else (6 if a[0].pv_fp8 else (5 if a[0].dtype == DTYPE_BF16 else 4))),

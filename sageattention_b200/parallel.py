@@ -263,9 +263,197 @@ def _ulysses_b1_p2p(q, k, v, group, world, attn_fn, head_chunks, kwargs):
     return out
 
 
+# ---------------------------------------------------------------------------------------------------
+# Quantised payload: the pre-pass runs on the sequence shards BEFORE the all-to-all, so INT8 Q / K codes,
+# e4m3 V codes and their scales travel (1 byte per element instead of 2) and the rank that receives them goes straight
+# into the attention kernel.  What makes the codes those of the one-GPU call:
+#   * quantisation groups are blocks of the GLOBAL sequence (128 q rows, 64 k rows, 16-token V permutation groups), and
+#     sequence shards are not aligned to them (Wan2.1: 75 600 / 8 = 9 450 rows).  So ownership is re-cut on 128-row
+#     boundaries: rank r quantises global rows [r*M, (r+1)*M), M = ceil128(n_loc); the rows it lacks - at most
+#     (r+1)*(M - n_loc) < 128*P - come from rank r+1 in one small neighbour exchange (the "halo");
+#   * K's mean and V's channel range are global: every rank reduces its own rows (sage_col_sum_absmax), the [2, H, D]
+#     partials are all-gathered and folded in rank order on every rank (deterministic; Q and V codes and all scales are
+#     bit-identical to one GPU, K's mean can differ from the one-GPU summation order in the last bit of a channel);
+#   * the quantisers write straight into the send layout: with B = 1 the batch dimension of the C-ABI tensors is free,
+#     so "batch" = destination rank (stride = its head group) and one launch per tensor produces [P, M, heads/P, D].
+# Inbound collectives: one for the Q / K codes (token-major, read in place by the attention kernel through strided TMA
+# maps), one for V^T codes + the Q / K scales.  The way back is the 16-bit output as before.
+class _Q8CudaOps:
+    """The device half of the quantised-payload path, over the C ABI (tests/test_parallel_cpu.py substitutes a CPU
+    stand-in with the same methods to exercise the host logic over gloo)."""
+    scale_max = 448.0   # sageattn: pv_accum_dtype "fp32+fp32" (/root/reference/sageattention/core.py:818-820)
+
+    def stats(self, k, v):
+        """[2, H, D] f32: column sums of this shard's K rows, max|v| per channel of its V rows."""
+        from . import _lib
+        from .quant import _dtype_code, _on_device, _stream
+        lib = _lib.load()
+        _, n, h, d = k.shape
+        out = torch.empty((2, h, d), dtype=torch.float32, device=k.device)
+        ws = torch.empty(lib.sage_seq_mean_workspace_bytes(1, h, n, d), dtype=torch.uint8, device=k.device)
+        with _on_device(k.device):
+            for x, so, ao in ((k, out[0].data_ptr(), None), (v, None, out[1].data_ptr())):
+                x4 = _lib.Tensor4(x.data_ptr(), x.stride(0), x.stride(2), x.stride(1))
+                _lib.check(lib.sage_col_sum_absmax(x4, so, ao, 1, h, n, d, _dtype_code(x), ws.data_ptr(), _stream(x)))
+        return out
+
+    def mean_from_sum(self, ksum, n_total, dtype):
+        # sage_seq_mean's arithmetic (torch's mean): f32 sum * (float(outputs) / float(elements)), rounded to the dtype
+        h, d = ksum.shape
+        factor = torch.tensor(float(h * d), dtype=torch.float32) / torch.tensor(float(h * d) * n_total, dtype=torch.float32)
+        return (ksum * factor.item()).to(dtype)
+
+    def quant_rows(self, x, rows, km, is_key, world, out, scale):
+        """x: [M, H, D] staging rows (the first `rows` valid).  out: int8 [P, M, H/P, D] view (any strides, rows
+        contiguous), scale: f32 [P, H/P, per_head] contiguous - per_thread codes of heads [p*H/P, (p+1)*H/P) go to
+        out[p] / scale[p]."""
+        from . import _lib
+        from .quant import _dtype_code, _on_device, _stream
+        lib = _lib.load()
+        m, h, d = x.shape
+        hp = h // world
+        x4 = _lib.Tensor4(x.data_ptr(), hp * x.stride(1), x.stride(1), x.stride(0))
+        o4 = _lib.Tensor4(out.data_ptr(), out.stride(0), out.stride(2), out.stride(1))
+        with _on_device(x.device):
+            _lib.check(lib.sage_quant_per_thread_int8(x4, km.data_ptr() if km is not None else None, o4, scale.data_ptr(),
+                                                      world, hp, rows, d, _dtype_code(x), 1 if is_key else 0,
+                                                      64 if is_key else 32, _stream(x)))
+
+    def v_convert(self, x, rows, absmax, world, out, v_scale):
+        """x: [M, H, D] staging rows of V.  out: uint8 [P, H/P, D, M] view; v_scale: f32 [H, D] (absmax / scale_max)."""
+        from . import _lib
+        from .quant import _dtype_code, _on_device, _stream
+        lib = _lib.load()
+        m, h, d = x.shape
+        hp = h // world
+        x4 = _lib.Tensor4(x.data_ptr(), hp * x.stride(1), x.stride(1), x.stride(0))
+        n_stat = (rows + 127) // 128 * 128
+        with _on_device(x.device):
+            _lib.check(lib.sage_v_fp8_from_absmax(x4, out.data_ptr(), out.stride(0), out.stride(1), out.stride(2),
+                                                  absmax.data_ptr(), v_scale.data_ptr(), world, hp, rows, n_stat, d,
+                                                  _dtype_code(x), self.scale_max, _stream(x)))
+
+    def attention(self, q8, k8, v8, q_scale, k_scale, v_scale, out_dtype, is_causal, sm_scale):
+        """q8 / k8: int8 [1, N, h, D] (strided), v8: uint8 [h, D, Npad]; -> o [1, N, h, D]."""
+        from . import _lib, core
+        _, n, h, d = q8.shape
+        o = torch.empty((1, n, h, d), dtype=out_dtype, device=q8.device)
+        v4 = v8.view(torch.float8_e4m3fn).unsqueeze(0).transpose(1, 2)   # "NHD" form of v_fp8: [B, D, H, Npad]
+        core._launch(True, q8, k8, v4, o, q_scale, k_scale, v_scale, None, "NHD", is_causal, _lib.GRAN_PER_THREAD, 32,
+                     sm_scale, False)
+        return o
+
+
+def q8_geometry(n: int, world: int):
+    """Ownership of the quantised-payload path for shards of n rows: (M, [rows owned by rank 0..P-1]) or None when the
+    shards are too short for a one-neighbour halo."""
+    m = (n + 127) // 128 * 128
+    if world * (m - n) > n:
+        return None
+    total = world * n
+    own = [max(0, min((r + 1) * m, total) - r * m) for r in range(world)]
+    return m, own
+
+
+def _scale_counts(rows: int):
+    """per_thread scale entries per head for `rows` rows: (query: 8 per 32-row warp tile of whole 128-row blocks,
+    key: 4 per 64-row block) - include/sage_b200.h, sage_quant_per_thread_int8."""
+    return (rows + 127) // 128 * 32, (rows + 63) // 64 * 4
+
+
+def _ulysses_b1_q8(q, k, v, group, world, ops, is_causal=False, sm_scale=None):
+    rank = dist.get_rank(group)
+    _, n, h, d = q.shape
+    hp = h // world
+    m, own = q8_geometry(n, world)
+    total = world * n
+    mine = own[rank]
+    dev, dt = q.device, q.dtype
+    peer = (lambda r: dist.get_global_rank(group, r)) if group is not None else (lambda r: r)
+
+    # 1. partial statistics of the local rows -> global K mean and V range (same fold order on every rank)
+    part = ops.stats(k, v)
+    allp = [torch.empty_like(part) for _ in range(world)]
+    dist.all_gather(allp, part, group=group)
+    ksum, vmax = allp[0][0].clone(), allp[0][1].clone()
+    for r in range(1, world):
+        ksum += allp[r][0]
+        vmax = torch.maximum(vmax, allp[r][1])
+    km = ops.mean_from_sum(ksum, total, dt)
+
+    # 2. staging [3, M, H, D]: the rows this rank owns = the tail of its shard + the head of the next rank's
+    give = rank * (m - n)                 # my first rows belong to rank - 1
+    keep = n - give
+    halo = mine - keep
+    stage = torch.empty((3, m, h, d), dtype=dt, device=dev)
+    ops_p2p = []
+    for i, x in enumerate((q, k, v)):
+        if give > 0:
+            ops_p2p.append(dist.P2POp(dist.isend, x[0, :give], peer(rank - 1), group))
+        if halo > 0:
+            ops_p2p.append(dist.P2POp(dist.irecv, stage[i, keep:mine], peer(rank + 1), group))
+    works = dist.batch_isend_irecv(ops_p2p) if ops_p2p else []
+    for i, x in enumerate((q, k, v)):
+        stage[i, :keep].copy_(x[0, give:])
+    for w in works:
+        w.wait()
+
+    # 3. quantise into the send layout
+    nsq, nsk = _scale_counts(m)           # per-head scale capacity of a chunk (a full 128-aligned block of M rows)
+    nsq_r, nsk_r = _scale_counts(mine)
+    cv = hp * d * m + hp * (nsq + nsk) * 4          # bytes per destination of the V / scales buffer
+    qk_send = torch.empty((world, m, 2, hp, d), dtype=torch.int8, device=dev)
+    vs_send = torch.empty((world, cv), dtype=torch.uint8, device=dev)
+    qs_tmp = torch.empty((world, hp, nsq_r), dtype=torch.float32, device=dev)
+    ks_tmp = torch.empty((world, hp, nsk_r), dtype=torch.float32, device=dev)
+    v_scale = torch.empty((h, d), dtype=torch.float32, device=dev)
+    ops.quant_rows(stage[0], mine, None, False, world, qk_send[:, :, 0], qs_tmp)
+    ops.quant_rows(stage[1], mine, km, True, world, qk_send[:, :, 1], ks_tmp)
+    ops.v_convert(stage[2], mine, vmax, world, vs_send[:, :hp * d * m].view(world, hp, d, m), v_scale)
+    tail = vs_send[:, hp * d * m:].view(torch.float32)          # [P, hp * (nsq + nsk)]
+    tail[:, :hp * nsq_r].copy_(qs_tmp.view(world, hp * nsq_r))
+    tail[:, hp * nsq:hp * nsq + hp * nsk_r].copy_(ks_tmp.view(world, hp * nsk_r))
+
+    # 4. the two inbound collectives
+    qk_recv = torch.empty_like(qk_send)
+    vs_recv = torch.empty_like(vs_send)
+    dist.all_to_all_single(qk_recv, qk_send, group=group)
+    dist.all_to_all_single(vs_recv, vs_send, group=group)
+
+    # 5. this rank's heads of the whole sequence: codes in place, V^T and the scales re-assembled by source rank
+    qk = qk_recv.view(1, world * m, 2, hp, d)
+    q8, k8 = qk[:, :total, 0], qk[:, :total, 1]
+    v8 = torch.empty((hp, d, world * m), dtype=torch.uint8, device=dev)
+    v8.view(hp, d, world, m).copy_(vs_recv[:, :hp * d * m].view(world, hp, d, m).permute(1, 2, 0, 3))
+    tq, tk = _scale_counts(total)
+    q_scale = torch.empty((1, hp, tq), dtype=torch.float32, device=dev)
+    k_scale = torch.empty((1, hp, tk), dtype=torch.float32, device=dev)
+    rtail = vs_recv[:, hp * d * m:].view(torch.float32)
+    oq = ok = 0
+    for s_ in range(world):
+        if own[s_] == 0:
+            continue
+        cq, ck = _scale_counts(own[s_])
+        q_scale[0, :, oq:oq + cq].copy_(rtail[s_, :hp * cq].view(hp, cq))
+        k_scale[0, :, ok:ok + ck].copy_(rtail[s_, hp * nsq:hp * nsq + hp * ck].view(hp, ck))
+        oq += cq
+        ok += ck
+    assert oq == tq and ok == tk, "scale bookkeeping"
+    if sm_scale is None:
+        sm_scale = d ** -0.5
+    o = ops.attention(q8, k8, v8, q_scale, k_scale, v_scale[rank * hp:(rank + 1) * hp].contiguous(), dt, is_causal,
+                      sm_scale)
+
+    # 6. the way back: 16-bit output, one all-to-all + the head interleave
+    r_ = _a2a_heads_out(o, group, world)
+    out = torch.empty((1, n, h, d), dtype=dt, device=dev)
+    out.view(n, world, hp, d).copy_(r_.transpose(0, 1))
+    return out
+
+
 def ulysses_sageattn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, group=None,
                      attn_fn: Optional[Callable] = None, head_chunks: int = 1, transport: str = "nccl",
-                     comm_sms: int = 0, **kwargs) -> torch.Tensor:
+                     comm_sms: int = 0, payload: str = "16bit", _q8_ops=None, **kwargs) -> torch.Tensor:
     """Sequence-parallel attention.  q, k, v: this rank's sequence block, "NHD" layout
     [B, N/P, H, D] (all ranks hold equally long blocks; pad the sequence to a multiple of P first).
     Returns this rank's block of the output, [B, N/P, H, D].  kwargs go to the attention function
@@ -276,10 +464,14 @@ def ulysses_sageattn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, group=No
     `head_chunks`: with B = 1, how many groups the rank's heads are split into so that the all-to-alls of
     one group overlap the attention of another (1 = no overlap).
     `comm_sms`: with head_chunks > 1 and NCCL, how many SMs the persistent attention grid leaves free, so that
-    NCCL's all-to-all kernels (which need SMs) really run next to the attention of another group."""
+    NCCL's all-to-all kernels (which need SMs) really run next to the attention of another group.
+    `payload`: "16bit" ships q, k, v as they are and quantises after the all-to-all; "int8" (B = 1 self-attention with
+    head_dim 64 / 128 through the default `sageattn`) quantises the sequence shards first and ships INT8 / e4m3 codes
+    and scales - half the inbound bytes (see _ulysses_b1_q8); shapes it does not cover fall back to "16bit"."""
     if kwargs.pop("return_lse", False):
         raise ValueError("ulysses_sageattn does not return the LSE")
     kwargs.pop("tensor_layout", None)
+    default_attn = attn_fn is None
     if attn_fn is None:
         from .core import sageattn as attn_fn
     world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -288,6 +480,14 @@ def ulysses_sageattn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, group=No
     h = q.size(2)
     if h % world or k.size(2) % world:
         raise ValueError(f"head counts ({h}, {k.size(2)}) must be divisible by the world size {world}")
+    if payload not in ("16bit", "int8"):
+        raise ValueError(f"unknown payload {payload!r}")
+    if payload == "int8" and q.size(0) == 1 and q.shape == k.shape == v.shape and q.size(3) in (64, 128) and \
+            all(t.is_contiguous() for t in (q, k, v)) and q8_geometry(q.size(1), world) is not None and \
+            (_q8_ops is not None or (default_attn and q.is_cuda and set(kwargs) <= {"is_causal", "sm_scale", "smooth_k"}
+                                     and kwargs.get("smooth_k", True))):
+        ops = _q8_ops if _q8_ops is not None else _Q8CudaOps()
+        return _ulysses_b1_q8(q, k, v, group, world, ops, bool(kwargs.get("is_causal", False)), kwargs.get("sm_scale"))
     if q.size(0) == 1 and k.size(0) == 1 and all(t.is_contiguous() for t in (q, k, v)):
         # the DiT case (B = 1): communication pipelined against attention over groups of heads
         if transport == "p2p" and (k.size(1) != q.size(1) or v.size(1) != k.size(1)):

@@ -75,3 +75,119 @@ def test_two_devices_from_one_process():
         outs.append((o8.cpu(), o16.cpu()))
     for o8, o16 in outs[1:]:
         assert torch.equal(o8, outs[0][0]) and torch.equal(o16, outs[0][1])
+
+
+# ---------------------------------------------------------------------------------------------------
+# Quantised-payload Ulysses.  The device half runs on ONE GPU (these tests are not skipped on the
+# driver's 1-GPU box): the C-ABI entry points that the path adds, and the existing quantisers driven through the
+# "batch = destination rank" strides, against the one-GPU quantisers.  The end-to-end 2-rank test follows.
+def _q8_inputs(n, h, d, dtype=torch.bfloat16, seed=3):
+    g = torch.Generator().manual_seed(seed)
+    q = torch.randn(1, n, h, d, generator=g).to(dtype).cuda()
+    k = (torch.randn(1, n, h, d, generator=g) + torch.randn(1, 1, h, d, generator=g)).to(dtype).cuda()
+    v = (torch.randn(1, n, h, d, generator=g) * (1 + torch.rand(1, 1, h, d, generator=g))).to(dtype).cuda()
+    return q, k, v
+
+
+@pytest.mark.parametrize("d", [64, 128])
+@pytest.mark.parametrize("n", [1000, 1152])
+def test_q8_device_half_matches_one_gpu_quantisers(n, d):
+    from sageattention_b200 import parallel, quant
+    ops = parallel._Q8CudaOps()
+    h, world = 6, 3
+    hp = h // world
+    q, k, v = _q8_inputs(n, h, d)
+    # statistics: column sums / channel range of a shard
+    st = ops.stats(k, v)
+    ref_sum = k[0].double().sum(0)
+    assert torch.allclose(st[0].double(), ref_sum, rtol=1e-5, atol=1e-3)
+    assert torch.equal(st[1], v[0].float().abs().amax(0))
+    km = ops.mean_from_sum(st[0], n, k.dtype)
+    # the one-GPU mean (torch arithmetic) may differ from the folded sum in the last bit of a channel, no more
+    km1 = quant.seq_mean(k, "NHD")[0]
+    assert (km.float() - km1.float()).abs().max() <= 2 * torch.finfo(k.dtype).eps * km1.float().abs().max()
+    # codes and scales, written through "batch = destination rank" strides into a [P, M, 2, hp, D] send buffer
+    m = (n + 127) // 128 * 128
+    send = torch.zeros((world, m, 2, hp, d), dtype=torch.int8, device="cuda")
+    nsq, nsk = parallel._scale_counts(n)
+    qs = torch.empty((world, hp, nsq), device="cuda")
+    ks = torch.empty((world, hp, nsk), device="cuda")
+    stage = torch.zeros((3, m, h, d), dtype=q.dtype, device="cuda")
+    for i, x in enumerate((q, k, v)):
+        stage[i, :n] = x[0]
+    ops.quant_rows(stage[0], n, None, False, world, send[:, :, 0], qs)
+    ops.quant_rows(stage[1], n, km, True, world, send[:, :, 1], ks)
+    q8, q_scale, k8, k_scale = quant.per_thread_int8(q, k, km.reshape(1, 1, h, d), tensor_layout="NHD")
+    assert torch.equal(send[:, :n, 0].permute(1, 0, 2, 3).reshape(n, h, d), q8[0])
+    assert torch.equal(send[:, :n, 1].permute(1, 0, 2, 3).reshape(n, h, d), k8[0])
+    assert torch.equal(qs.reshape(h, nsq), q_scale[0]) and torch.equal(ks.reshape(h, nsk), k_scale[0])
+    # V: conversion with a caller-provided range == the one-GPU per_channel_fp8 (codes, scales; padding zeroed)
+    v8 = torch.full((world, hp, d, m), 0x7F, dtype=torch.uint8, device="cuda")
+    v_scale = torch.empty((h, d), device="cuda")
+    ops.v_convert(stage[2], n, st[1], world, v8, v_scale)
+    n_stat = (n + 127) // 128 * 128
+    r8, r_scale, _ = quant.per_channel_fp8(v, tensor_layout="NHD", scale_max=448.0, smooth_v=False, _n_stat=n_stat)
+    npad = r8.size(-1)
+    assert torch.equal(v8.reshape(h, d, m)[:, :, :npad], r8[0].view(torch.uint8).permute(1, 0, 2))
+    assert torch.equal(v_scale, r_scale[0])
+    # the attention kernel on those buffers as the receiving rank sees them == the operator's own two-call path
+    from sageattention_b200 import _lib, core
+    o_ref = torch.empty((1, n, h, d), dtype=q.dtype, device="cuda")
+    core._launch(True, q8, k8, r8, o_ref, q_scale, k_scale, r_scale, None, "NHD", False, _lib.GRAN_PER_THREAD, 32,
+                 d ** -0.5, False)
+    for p in range(world):
+        o = ops.attention(send[p:p + 1, :n, 0], send[p:p + 1, :n, 1], v8[p], qs[p:p + 1], ks[p:p + 1],
+                          v_scale[p * hp:(p + 1) * hp].contiguous(), q.dtype, False, d ** -0.5)
+        assert torch.equal(o, o_ref[:, :, p * hp:(p + 1) * hp])
+
+
+def _q8_worker(rank, world, port, n, h, d, causal, q_out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        import sageattention_b200 as sb
+        from sageattention_b200 import parallel
+        q, k, v = _q8_inputs(n, h, d)
+        full = sb.sageattn(q, k, v, tensor_layout="NHD", is_causal=causal)
+        nl = n // world
+        sl = slice(rank * nl, (rank + 1) * nl)
+        args = (q[:, sl].contiguous(), k[:, sl].contiguous(), v[:, sl].contiguous())
+        o = parallel.ulysses_sageattn(*args, payload="int8", is_causal=causal)
+        o2 = parallel.ulysses_sageattn(*args, payload="int8", is_causal=causal)     # buffers of a second call
+        torch.cuda.synchronize()
+        ref = torch.nn.functional.scaled_dot_product_attention(
+            q.float().transpose(1, 2), k.float().transpose(1, 2), v.float().transpose(1, 2),
+            is_causal=causal).transpose(1, 2)[:, sl]
+        f = lambda a, b_: torch.nn.functional.cosine_similarity(a.float().flatten(), b_.float().flatten(), dim=0).item()
+        l1 = lambda a, b_: ((a.float() - b_.float()).abs().sum() / b_.float().abs().sum()).item()
+        q_out.put((rank, tuple(o.shape), bool(torch.equal(o, o2)), f(o, full[:, sl]), l1(o, full[:, sl]),
+                   l1(o, ref), l1(full[:, sl], ref), (o != full[:, sl]).float().mean().item()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("n,h,d,causal", [(2 * 1100, 8, 128, False), (2 * 1024, 4, 64, True), (2 * 1332, 4, 128, True)])
+def test_ulysses_quantised_payload_two_gpus(n, h, d, causal):
+    """payload="int8" on 2 GPUs against the one-GPU operator on the gathered inputs: Q / V codes and all scales are the
+    one-GPU ones and K's mean can differ in the last bit of a channel (other summation order), so the outputs agree far
+    inside the quantisation noise - and the error against fp32 attention is the one-GPU operator's."""
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    ctx = mp.get_context("spawn")
+    q_out = ctx.Queue()
+    port = 29900 + os.getpid() % 1000 + d
+    procs = [ctx.Process(target=_q8_worker, args=(r, 2, port, n, h, d, causal, q_out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q_out.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, shape, repeat_same, cos, l1_full, l1_ref, l1_full_ref, frac_diff in res:
+        print(f"rank {rank}: cos {cos:.7f} rel-L1 vs one GPU {l1_full:.2e}; vs fp32 {l1_ref:.4f} (one GPU {l1_full_ref:.4f}); "
+              f"elements differing {frac_diff:.3%}")
+        assert shape == (1, n // 2, h, d)
+        assert repeat_same
+        assert cos >= 0.9999 and l1_full <= 5e-3
+        assert l1_ref <= 1.02 * l1_full_ref + 1e-4
