@@ -109,6 +109,14 @@ int sage_quant_per_thread_int8(sage_tensor4 x, const void* mean, sage_tensor4 ou
                                int B, int H, int N, int D, int dtype, int is_key, int tile,
                                void* stream);
 
+/* sage_quant_per_thread_int8 with an explicit distance scale_per_bh (>= the entries N rows produce) between the scale
+ * rows of consecutive (b, h): a caller that quantises one sequence in several calls over row ranges that start on 128-row
+ * boundaries points each call at its columns of one [B, H, scale_per_bh] array (same reference arithmetic,
+ * /root/reference/sageattention/triton/quant_per_thread.py:22-102). */
+int sage_quant_per_thread_int8_strided(sage_tensor4 x, const void* mean, sage_tensor4 out, float* scale,
+                                       int B, int H, int N, int D, int dtype, int is_key, int tile,
+                                       int scale_per_bh, void* stream);
+
 /* K smoothing and quantisation in one launch (a thread-block cluster per (b,h) slice reads K once
  * from HBM): mean_out[b,h,:] = dtype(mean over the sequence), then the codes and scales that
  * sage_quant_int8(block = 64, mean) (per_thread = 0) or sage_quant_per_thread_int8(is_key = 1, mean)

@@ -59,6 +59,8 @@ SIGNATURES = {
                                 c_int, c_int, c_f32, c_vp]),
     "sage_quant_per_thread_int8": (c_int, [Tensor4, c_vp, Tensor4, c_vp, c_int, c_int, c_int, c_int, c_int,
                                            c_int, c_int, c_vp]),
+    "sage_quant_per_thread_int8_strided": (c_int, [Tensor4, c_vp, Tensor4, c_vp, c_int, c_int, c_int, c_int, c_int,
+                                                   c_int, c_int, c_int, c_vp]),
     "sage_smooth_quant_k_int8": (c_int, [Tensor4, c_vp, Tensor4, c_vp, c_int, c_int, c_int, c_int, c_int,
                                          c_int, c_int, c_vp]),
     "sage_prepass_qk_int8": (c_int, [Tensor4, Tensor4, Tensor4, Tensor4, c_vp, c_vp, c_vp] + [c_int] * 12 + [c_vp]),
@@ -91,7 +93,7 @@ KERNELS_PER_CALL = {
     # smooth_v: statistics + conversion; otherwise one cluster launch
     "sage_per_channel_fp8": (lambda a: 2 if a[14] else 1),
     "sage_attn_i8_f16": 1, "sage_attn_i8_f8": 1,
-    "sage_per_channel_fp8_flat": 2, "sage_col_sum_absmax": 1, "sage_v_fp8_from_absmax": 1,
+    "sage_per_channel_fp8_flat": 2, "sage_col_sum_absmax": 1, "sage_quant_per_thread_int8_strided": 1, "sage_v_fp8_from_absmax": 1,
     # prologue + attention; above 65 536 kv rows the prologue is flat launches (K mean, Q, K, V range, V conversion /
     # f16 copy of a bf16 V)
     "sage_sageattn_fwd": (lambda a: 2 if a[0].Nk <= 65536 else (6 if a[0].pv_fp8 else (5 if a[0].dtype == DTYPE_BF16 else 4))),

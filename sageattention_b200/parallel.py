@@ -304,23 +304,25 @@ class _Q8CudaOps:
         return (ksum * factor.item()).to(dtype)
 
     def quant_rows(self, x, rows, km, is_key, world, out, scale):
-        """x: [M, H, D] staging rows (the first `rows` valid).  out: int8 [P, M, H/P, D] view (any strides, rows
-        contiguous), scale: f32 [P, H/P, per_head] contiguous - per_thread codes of heads [p*H/P, (p+1)*H/P) go to
-        out[p] / scale[p]."""
+        """x: [>= rows, H, D] rows starting on a 128-row boundary of the global sequence.  out: int8 [P, >= rows, H/P, D]
+        view (any strides, rows contiguous), scale: f32 [P, H/P, entries] view with any head stride - per_thread codes
+        and scales of heads [p*H/P, (p+1)*H/P) go to out[p] / scale[p]."""
         from . import _lib
         from .quant import _dtype_code, _on_device, _stream
         lib = _lib.load()
         m, h, d = x.shape
         hp = h // world
+        assert scale.stride(2) == 1 and scale.stride(0) == hp * scale.stride(1)
         x4 = _lib.Tensor4(x.data_ptr(), hp * x.stride(1), x.stride(1), x.stride(0))
         o4 = _lib.Tensor4(out.data_ptr(), out.stride(0), out.stride(2), out.stride(1))
         with _on_device(x.device):
-            _lib.check(lib.sage_quant_per_thread_int8(x4, km.data_ptr() if km is not None else None, o4, scale.data_ptr(),
-                                                      world, hp, rows, d, _dtype_code(x), 1 if is_key else 0,
-                                                      64 if is_key else 32, _stream(x)))
+            _lib.check(lib.sage_quant_per_thread_int8_strided(
+                x4, km.data_ptr() if km is not None else None, o4, scale.data_ptr(), world, hp, rows, d, _dtype_code(x),
+                1 if is_key else 0, 64 if is_key else 32, scale.stride(1), _stream(x)))
 
     def v_convert(self, x, rows, absmax, world, out, v_scale):
-        """x: [M, H, D] staging rows of V.  out: uint8 [P, H/P, D, M] view; v_scale: f32 [H, D] (absmax / scale_max)."""
+        """x: [>= rows, H, D] rows of V starting on a 128-row boundary.  out: uint8 [P, H/P, D, >= ceil128(rows)] view;
+        v_scale: f32 [H, D] (absmax / scale_max)."""
         from . import _lib
         from .quant import _dtype_code, _on_device, _stream
         lib = _lib.load()
@@ -371,74 +373,95 @@ def _ulysses_b1_q8(q, k, v, group, world, ops, is_causal=False, sm_scale=None):
     dev, dt = q.device, q.dtype
     peer = (lambda r: dist.get_global_rank(group, r)) if group is not None else (lambda r: r)
 
-    # 1. partial statistics of the local rows -> global K mean and V range (same fold order on every rank)
-    part = ops.stats(k, v)
-    allp = [torch.empty_like(part) for _ in range(world)]
-    dist.all_gather(allp, part, group=group)
-    ksum, vmax = allp[0][0].clone(), allp[0][1].clone()
-    for r in range(1, world):
-        ksum += allp[r][0]
-        vmax = torch.maximum(vmax, allp[r][1])
-    km = ops.mean_from_sum(ksum, total, dt)
-
-    # 2. staging [3, M, H, D]: the rows this rank owns = the tail of its shard + the head of the next rank's
+    # 1. the rows this rank owns = the tail of its shard (from local row `give`) + the head of the next rank's (the
+    #    halo).  Whole 128-row blocks that lie inside the shard are quantised where they are; the rest (< 128 local rows
+    #    + the halo) goes through a small staging buffer.  The neighbour exchange is issued first: it runs under the
+    #    statistics kernels.
     give = rank * (m - n)                 # my first rows belong to rank - 1
-    keep = n - give
-    halo = mine - keep
-    stage = torch.empty((3, m, h, d), dtype=dt, device=dev)
+    keep = n - give                       # local rows I own
+    halo = mine - keep                    # rows of rank + 1 I own
+    main = keep // 128 * 128 if halo > 0 else keep   # (no halo: the shard's tail is the sequence's, one direct call)
+    edge = mine - main                    # rows through the staging buffer
+    stage = torch.empty((3, max(edge, 1), h, d), dtype=dt, device=dev)
     ops_p2p = []
     for i, x in enumerate((q, k, v)):
         if give > 0:
             ops_p2p.append(dist.P2POp(dist.isend, x[0, :give], peer(rank - 1), group))
         if halo > 0:
-            ops_p2p.append(dist.P2POp(dist.irecv, stage[i, keep:mine], peer(rank + 1), group))
+            ops_p2p.append(dist.P2POp(dist.irecv, stage[i, keep - main:edge], peer(rank + 1), group))
     works = dist.batch_isend_irecv(ops_p2p) if ops_p2p else []
-    for i, x in enumerate((q, k, v)):
-        stage[i, :keep].copy_(x[0, give:])
-    for w in works:
-        w.wait()
 
-    # 3. quantise into the send layout
-    nsq, nsk = _scale_counts(m)           # per-head scale capacity of a chunk (a full 128-aligned block of M rows)
-    nsq_r, nsk_r = _scale_counts(mine)
+    # 2. partial statistics of the local rows -> global K mean and V range (same fold on every rank)
+    part = ops.stats(k, v)
+    allp = torch.empty((world,) + tuple(part.shape), dtype=part.dtype, device=dev)
+    gathered = dist.all_gather(list(allp.unbind(0)), part, group=group, async_op=True)
+
+    # 3. quantise into the send layout (Q first: it needs no statistics and runs under the all-gather)
+    nsq, nsk = _scale_counts(m)           # per-head scale capacity of a chunk (M rows)
     cv = hp * d * m + hp * (nsq + nsk) * 4          # bytes per destination of the V / scales buffer
     qk_send = torch.empty((world, m, 2, hp, d), dtype=torch.int8, device=dev)
     vs_send = torch.empty((world, cv), dtype=torch.uint8, device=dev)
-    qs_tmp = torch.empty((world, hp, nsq_r), dtype=torch.float32, device=dev)
-    ks_tmp = torch.empty((world, hp, nsk_r), dtype=torch.float32, device=dev)
+    v_send = vs_send[:, :hp * d * m].view(world, hp, d, m)
+    tail = vs_send[:, hp * d * m:].view(torch.float32)          # [P, hp * nsq | hp * nsk]
+    # (the quantisers address scales as [batch = destination, head, entry] with a dense batch stride: own arrays, copied
+    # behind the V codes of every destination afterwards)
+    qs_send = torch.empty((world, hp, nsq), dtype=torch.float32, device=dev)
+    ks_send = torch.empty((world, hp, nsk), dtype=torch.float32, device=dev)
     v_scale = torch.empty((h, d), dtype=torch.float32, device=dev)
-    ops.quant_rows(stage[0], mine, None, False, world, qk_send[:, :, 0], qs_tmp)
-    ops.quant_rows(stage[1], mine, km, True, world, qk_send[:, :, 1], ks_tmp)
-    ops.v_convert(stage[2], mine, vmax, world, vs_send[:, :hp * d * m].view(world, hp, d, m), v_scale)
-    tail = vs_send[:, hp * d * m:].view(torch.float32)          # [P, hp * (nsq + nsk)]
-    tail[:, :hp * nsq_r].copy_(qs_tmp.view(world, hp * nsq_r))
-    tail[:, hp * nsq:hp * nsq + hp * nsk_r].copy_(ks_tmp.view(world, hp * nsk_r))
+    mq, mk = _scale_counts(main)
+    eq, ek = _scale_counts(edge)
+    if main > 0:
+        ops.quant_rows(q[0, give:give + main], main, None, False, world, qk_send[:, :main, 0], qs_send[:, :, :mq])
+    gathered.wait()
+    km = ops.mean_from_sum(allp[:, 0].sum(dim=0), total, dt)
+    vmax = allp[:, 1].amax(dim=0)
+    if main > 0:
+        ops.quant_rows(k[0, give:give + main], main, km, True, world, qk_send[:, :main, 1], ks_send[:, :, :mk])
+    if edge > 0:
+        for i, x in enumerate((q, k, v)):
+            if keep > main:
+                stage[i, :keep - main].copy_(x[0, give + main:])
+        for w in works:
+            w.wait()
+        ops.quant_rows(stage[0], edge, None, False, world, qk_send[:, main:, 0], qs_send[:, :, mq:mq + eq])
+        ops.quant_rows(stage[1], edge, km, True, world, qk_send[:, main:, 1], ks_send[:, :, mk:mk + ek])
+    else:
+        for w in works:
+            w.wait()
 
-    # 4. the two inbound collectives
+    # 4. the two inbound collectives; the codes of Q and K leave while V is still being converted
     qk_recv = torch.empty_like(qk_send)
     vs_recv = torch.empty_like(vs_send)
-    dist.all_to_all_single(qk_recv, qk_send, group=group)
+    qk_sent = dist.all_to_all_single(qk_recv, qk_send, group=group, async_op=True)
+    if main > 0:
+        ops.v_convert(v[0, give:give + main], main, vmax, world, v_send[..., :(main + 127) // 128 * 128], v_scale)
+    if edge > 0:
+        ops.v_convert(stage[2], edge, vmax, world, v_send[..., main:], v_scale)
+    tail[:, :hp * nsq].copy_(qs_send.view(world, hp * nsq))
+    tail[:, hp * nsq:].copy_(ks_send.view(world, hp * nsk))
     dist.all_to_all_single(vs_recv, vs_send, group=group)
+    qk_sent.wait()
 
-    # 5. this rank's heads of the whole sequence: codes in place, V^T and the scales re-assembled by source rank
+    # 5. this rank's heads of the whole sequence: codes in place, V^T and the scales re-assembled by source rank (every
+    #    source but the last non-empty one owns M rows)
     qk = qk_recv.view(1, world * m, 2, hp, d)
     q8, k8 = qk[:, :total, 0], qk[:, :total, 1]
     v8 = torch.empty((hp, d, world * m), dtype=torch.uint8, device=dev)
     v8.view(hp, d, world, m).copy_(vs_recv[:, :hp * d * m].view(world, hp, d, m).permute(1, 2, 0, 3))
     tq, tk = _scale_counts(total)
+    rtail = vs_recv[:, hp * d * m:].view(torch.float32)
+    rq = rtail[:, :hp * nsq].view(world, hp, nsq)
+    rk = rtail[:, hp * nsq:].view(world, hp, nsk)
+    nfull = sum(1 for o_ in own if o_ == m)
     q_scale = torch.empty((1, hp, tq), dtype=torch.float32, device=dev)
     k_scale = torch.empty((1, hp, tk), dtype=torch.float32, device=dev)
-    rtail = vs_recv[:, hp * d * m:].view(torch.float32)
-    oq = ok = 0
-    for s_ in range(world):
-        if own[s_] == 0:
-            continue
-        cq, ck = _scale_counts(own[s_])
-        q_scale[0, :, oq:oq + cq].copy_(rtail[s_, :hp * cq].view(hp, cq))
-        k_scale[0, :, ok:ok + ck].copy_(rtail[s_, hp * nsq:hp * nsq + hp * ck].view(hp, ck))
-        oq += cq
-        ok += ck
-    assert oq == tq and ok == tk, "scale bookkeeping"
+    q_scale[0, :, :nfull * nsq].view(hp, nfull, nsq).copy_(rq[:nfull].permute(1, 0, 2))
+    k_scale[0, :, :nfull * nsk].view(hp, nfull, nsk).copy_(rk[:nfull].permute(1, 0, 2))
+    if nfull < world and own[nfull] > 0:
+        cq, ck = _scale_counts(own[nfull])
+        q_scale[0, :, nfull * nsq:].copy_(rq[nfull, :, :cq])
+        k_scale[0, :, nfull * nsk:].copy_(rk[nfull, :, :ck])
+        assert nfull * nsq + cq == tq and nfull * nsk + ck == tk, "scale bookkeeping"
     if sm_scale is None:
         sm_scale = d ** -0.5
     o = ops.attention(q8, k8, v8, q_scale, k_scale, v_scale[rank * hp:(rank + 1) * hp].contiguous(), dt, is_causal,

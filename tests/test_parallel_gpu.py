@@ -121,6 +121,16 @@ def test_q8_device_half_matches_one_gpu_quantisers(n, d):
     assert torch.equal(send[:, :n, 0].permute(1, 0, 2, 3).reshape(n, h, d), q8[0])
     assert torch.equal(send[:, :n, 1].permute(1, 0, 2, 3).reshape(n, h, d), k8[0])
     assert torch.equal(qs.reshape(h, nsq), q_scale[0]) and torch.equal(ks.reshape(h, nsk), k_scale[0])
+    # the same in two calls (whole 128-row blocks where they lie + the remainder), each into its rows / scale columns
+    send2 = torch.zeros_like(send)
+    qs2, ks2 = torch.zeros_like(qs), torch.zeros_like(ks)
+    cut = 640
+    (cq, ck), (eq, ek) = parallel._scale_counts(cut), parallel._scale_counts(n - cut)
+    ops.quant_rows(stage[0], cut, None, False, world, send2[:, :cut, 0], qs2[:, :, :cq])
+    ops.quant_rows(stage[0, cut:], n - cut, None, False, world, send2[:, cut:, 0], qs2[:, :, cq:cq + eq])
+    ops.quant_rows(stage[1], cut, km, True, world, send2[:, :cut, 1], ks2[:, :, :ck])
+    ops.quant_rows(stage[1, cut:], n - cut, km, True, world, send2[:, cut:, 1], ks2[:, :, ck:ck + ek])
+    assert torch.equal(send2[:, :n], send[:, :n]) and torch.equal(qs2, qs) and torch.equal(ks2, ks)
     # V: conversion with a caller-provided range == the one-GPU per_channel_fp8 (codes, scales; padding zeroed)
     v8 = torch.full((world, hp, d, m), 0x7F, dtype=torch.uint8, device="cuda")
     v_scale = torch.empty((h, d), device="cuda")
@@ -130,6 +140,10 @@ def test_q8_device_half_matches_one_gpu_quantisers(n, d):
     npad = r8.size(-1)
     assert torch.equal(v8.reshape(h, d, m)[:, :, :npad], r8[0].view(torch.uint8).permute(1, 0, 2))
     assert torch.equal(v_scale, r_scale[0])
+    v8b = torch.full_like(v8, 0x7F)
+    ops.v_convert(stage[2], cut, st[1], world, v8b[..., :cut], v_scale)
+    ops.v_convert(stage[2, cut:], n - cut, st[1], world, v8b[..., cut:], v_scale)
+    assert torch.equal(v8b[..., :npad], v8[..., :npad])
     # the attention kernel on those buffers as the receiving rank sees them == the operator's own two-call path
     from sageattention_b200 import _lib, core
     o_ref = torch.empty((1, n, h, d), dtype=q.dtype, device="cuda")
