@@ -344,6 +344,21 @@ def run_sp(dev, world, rank, barrier, max_over_ranks, transport="nccl", chunks=1
                     "pre-pass, which runs inside the attention call there)"}
     except Exception as e:  # the record of the default path must survive a failure here
         rec["int8_payload"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+    # and with the quantisers storing straight into the peers' symmetric-memory arenas over NVLink: no inbound collective
+    try:
+        full9 = lambda: parallel.ulysses_sageattn(qs, ks_, vs_, payload="int8", transport="p2p", is_causal=False)
+        comm9 = lambda: parallel.ulysses_sageattn(qs, ks_, vs_, payload="int8", transport="p2p", _q8_ops=_NullAttention(),
+                                                  is_causal=False)
+        ms9 = timed(full9)
+        comm9_ms = timed(comm9)
+        rec["int8_payload_peer_stores"] = {
+            "ms": round(ms9, 3), "tops": round(flops / (ms9 * 1e-3) * 1e-12, 1),
+            "comm_and_prepass_ms": round(comm9_ms, 3), "efficiency": round(one_ms / (world * ms9), 4),
+            "note": "quantiser launches write INT8 / e4m3 codes and scales into the destination ranks' arenas (one base "
+                    "pointer per destination); two signal-pad barriers; statistics all-gather, halo and the 16-bit way "
+                    "back over NCCL"}
+    except Exception as e:
+        rec["int8_payload_peer_stores"] = {"error": f"{type(e).__name__}: {e}"[:300]}
     return rec
 
 

@@ -197,6 +197,19 @@ int sage_v_fp8_from_absmax(sage_tensor4 v, uint8_t* v_out, int64_t vo_stride_b, 
                            const float* absmax, float* v_scale_out, int B, int H, int N, int n_stat, int D, int dtype,
                            float scale_max, void* stream);
 
+/* The two calls above with ONE OUTPUT BASE POINTER PER "BATCH" (B <= 16): in the quantised-payload sequence-parallel path
+ * the batch dimension is the destination rank, and with out_ptrs / scale_ptrs (HOST arrays of B device pointers) aimed at
+ * the peers' symmetric-memory receive buffers the quantiser's stores travel over NVLink - quantiser and all-to-all in
+ * one launch, no NCCL kernel on the inbound path.  No counterpart in the reference (its sequence-parallel example ships
+ * 16-bit activations through xDiT, example/parallel_sageattn_cogvideo.py:43-52).  Codes of (b, h, n) go to
+ * out_ptrs[b] + h*out_stride_h + n*out_stride_n, scales to scale_ptrs[b] + h*scale_per_bh. */
+int sage_quant_per_thread_int8_peers(sage_tensor4 x, const void* mean, void* const* out_ptrs, int64_t out_stride_h,
+                                     int64_t out_stride_n, float* const* scale_ptrs, int B, int H, int N, int D,
+                                     int dtype, int is_key, int tile, int scale_per_bh, void* stream);
+int sage_v_fp8_from_absmax_peers(sage_tensor4 v, void* const* out_ptrs, int64_t vo_stride_h, int64_t vo_stride_d,
+                                 const float* absmax, float* v_scale_out, int B, int H, int N, int n_stat, int D,
+                                 int dtype, float scale_max, void* stream);
+
 /* Attention kernels.  q8/k8: int8 [B,H,N,D] via strides; scales laid out exactly as the reference
  * quantizers produce them; o: f16/bf16 via strides; lse: [B,Hq,Nq] fp32 or NULL (base-2, as the
  * reference kernels return it). */

@@ -77,6 +77,10 @@ SIGNATURES = {
     "sage_col_sum_absmax": (c_int, [Tensor4, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int, c_vp, c_vp]),
     "sage_v_fp8_from_absmax": (c_int, [Tensor4, c_vp, c_i64, c_i64, c_i64, c_vp, c_vp, c_int, c_int, c_int, c_int, c_int,
                                        c_int, c_f32, c_vp]),
+    "sage_quant_per_thread_int8_peers": (c_int, [Tensor4, c_vp, ctypes.POINTER(c_vp), c_i64, c_i64, ctypes.POINTER(c_vp),
+                                                 c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_vp]),
+    "sage_v_fp8_from_absmax_peers": (c_int, [Tensor4, ctypes.POINTER(c_vp), c_i64, c_i64, c_vp, c_vp, c_int, c_int, c_int,
+                                             c_int, c_int, c_int, c_f32, c_vp]),
     "sage_attn_i8_f16": (c_int, [ctypes.POINTER(AttnArgs), c_vp]),
     "sage_attn_i8_f8": (c_int, [ctypes.POINTER(AttnArgs), c_vp]),
     "sage_sageattn_fwd_workspace_bytes": (ctypes.c_size_t, [ctypes.POINTER(FwdArgs)]),
@@ -93,7 +97,8 @@ KERNELS_PER_CALL = {
     # smooth_v: statistics + conversion; otherwise one cluster launch
     "sage_per_channel_fp8": (lambda a: 2 if a[14] else 1),
     "sage_attn_i8_f16": 1, "sage_attn_i8_f8": 1,
-    "sage_per_channel_fp8_flat": 2, "sage_col_sum_absmax": 1, "sage_quant_per_thread_int8_strided": 1, "sage_v_fp8_from_absmax": 1,
+    "sage_per_channel_fp8_flat": 2, "sage_col_sum_absmax": 1, "sage_quant_per_thread_int8_strided": 1,
+    "sage_quant_per_thread_int8_peers": 1, "sage_v_fp8_from_absmax_peers": 1, "sage_v_fp8_from_absmax": 1,
     # prologue + attention; above 65 536 kv rows the prologue is flat launches (K mean, Q, K, V range, V conversion /
     # f16 copy of a bf16 V)
     "sage_sageattn_fwd": (lambda a: 2 if a[0].Nk <= 65536 else (6 if a[0].pv_fp8 else (5 if a[0].dtype == DTYPE_BF16 else 4))),

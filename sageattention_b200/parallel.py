@@ -335,6 +335,39 @@ class _Q8CudaOps:
                                                   absmax.data_ptr(), v_scale.data_ptr(), world, hp, rows, n_stat, d,
                                                   _dtype_code(x), self.scale_max, _stream(x)))
 
+    def quant_rows_peers(self, x, rows, km, is_key, world, out_ptrs, out_stride_h, out_stride_n, scale_ptrs,
+                         scale_per_bh):
+        """quant_rows with one output / scale base address per destination rank (ints: addresses inside the peers'
+        symmetric-memory arenas): the stores are the all-to-all."""
+        import ctypes
+        from . import _lib
+        from .quant import _dtype_code, _on_device, _stream
+        lib = _lib.load()
+        m, h, d = x.shape
+        hp = h // world
+        x4 = _lib.Tensor4(x.data_ptr(), hp * x.stride(1), x.stride(1), x.stride(0))
+        op = (ctypes.c_void_p * world)(*out_ptrs)
+        sp = (ctypes.c_void_p * world)(*scale_ptrs)
+        with _on_device(x.device):
+            _lib.check(lib.sage_quant_per_thread_int8_peers(
+                x4, km.data_ptr() if km is not None else None, op, out_stride_h, out_stride_n, sp, world, hp, rows, d,
+                _dtype_code(x), 1 if is_key else 0, 64 if is_key else 32, scale_per_bh, _stream(x)))
+
+    def v_convert_peers(self, x, rows, absmax, world, out_ptrs, out_stride_h, out_stride_d, v_scale):
+        import ctypes
+        from . import _lib
+        from .quant import _dtype_code, _on_device, _stream
+        lib = _lib.load()
+        m, h, d = x.shape
+        hp = h // world
+        x4 = _lib.Tensor4(x.data_ptr(), hp * x.stride(1), x.stride(1), x.stride(0))
+        op = (ctypes.c_void_p * world)(*out_ptrs)
+        n_stat = (rows + 127) // 128 * 128
+        with _on_device(x.device):
+            _lib.check(lib.sage_v_fp8_from_absmax_peers(x4, op, out_stride_h, out_stride_d, absmax.data_ptr(),
+                                                        v_scale.data_ptr(), world, hp, rows, n_stat, d, _dtype_code(x),
+                                                        self.scale_max, _stream(x)))
+
     def attention(self, q8, k8, v8, q_scale, k_scale, v_scale, out_dtype, is_causal, sm_scale):
         """q8 / k8: int8 [1, N, h, D] (strided), v8: uint8 [h, D, Npad]; -> o [1, N, h, D]."""
         from . import _lib, core
@@ -474,6 +507,99 @@ def _ulysses_b1_q8(q, k, v, group, world, ops, is_causal=False, sm_scale=None):
     return out
 
 
+def _ulysses_b1_q8_p2p(q, k, v, group, world, ops, is_causal=False, sm_scale=None):
+    """_ulysses_b1_q8 with NO inbound collective: every rank owns a symmetric-memory arena laid out as the attention
+    kernel wants its inputs ([P, M, 2, H/P, D] Q / K codes by source rank, V^T [H/P, D, P*M], scales [H/P, entries]), and
+    the quantisers of every rank store their codes and scales straight into the destinations' arenas over NVLink
+    (sage_quant_per_thread_int8_peers / sage_v_fp8_from_absmax_peers: one base pointer per destination) - the launch is
+    quantiser and all-to-all in one.  Two signal-pad barriers frame the stores (everybody has finished reading the
+    previous call's arena / everything has landed).  Statistics all-gather, halo and the way back as in _ulysses_b1_q8."""
+    group = group if group is not None else dist.group.WORLD
+    rank = dist.get_rank(group)
+    _, n, h, d = q.shape
+    hp = h // world
+    m, own = q8_geometry(n, world)
+    total = world * n
+    mine = own[rank]
+    dev, dt = q.device, q.dtype
+    peer = lambda r: dist.get_global_rank(group, r)
+    nsq, nsk = _scale_counts(m)
+    tq, tk = _scale_counts(total)
+    al = lambda x: (x + 255) // 256 * 256
+    off_v = al(world * m * 2 * hp * d)
+    off_qs = off_v + al(hp * d * world * m)
+    off_ks = off_qs + al(hp * tq * 4)
+    nbytes = off_ks + al(hp * tk * 4)
+    hdl, _ = _arena(nbytes, dev, group)
+    base = [hdl.get_buffer(p, (nbytes,), torch.uint8, 0).data_ptr() for p in range(world)]
+
+    give = rank * (m - n)
+    keep = n - give
+    halo = mine - keep
+    main = keep // 128 * 128 if halo > 0 else keep
+    edge = mine - main
+    stage = torch.empty((3, max(edge, 1), h, d), dtype=dt, device=dev)
+    ops_p2p = []
+    for i, x in enumerate((q, k, v)):
+        if give > 0:
+            ops_p2p.append(dist.P2POp(dist.isend, x[0, :give], peer(rank - 1), group))
+        if halo > 0:
+            ops_p2p.append(dist.P2POp(dist.irecv, stage[i, keep - main:edge], peer(rank + 1), group))
+    works = dist.batch_isend_irecv(ops_p2p) if ops_p2p else []
+    part = ops.stats(k, v)
+    allp = torch.empty((world,) + tuple(part.shape), dtype=part.dtype, device=dev)
+    gathered = dist.all_gather(list(allp.unbind(0)), part, group=group, async_op=True)
+
+    hdl.barrier()      # every rank's attention of the previous call has finished reading its arena
+    row = 2 * hp * d   # bytes between consecutive tokens of the Q / K code buffer
+    v_scale = torch.empty((h, d), dtype=torch.float32, device=dev)
+    mq, mk = _scale_counts(main)
+
+    def code_ptrs(is_key, row0):
+        return [b_ + rank * m * row + row0 * row + (hp * d if is_key else 0) for b_ in base]
+
+    def scale_ptrs(is_key, col0):
+        return [b_ + (off_ks + (rank * nsk + col0) * 4 if is_key else off_qs + (rank * nsq + col0) * 4) for b_ in base]
+
+    def v_ptrs(col0):
+        return [b_ + off_v + rank * m + col0 for b_ in base]
+
+    if main > 0:
+        ops.quant_rows_peers(q[0, give:give + main], main, None, False, world, code_ptrs(False, 0), d, row,
+                             scale_ptrs(False, 0), tq)
+    gathered.wait()
+    km = ops.mean_from_sum(allp[:, 0].sum(dim=0), total, dt)
+    vmax = allp[:, 1].amax(dim=0)
+    if main > 0:
+        ops.quant_rows_peers(k[0, give:give + main], main, km, True, world, code_ptrs(True, 0), d, row,
+                             scale_ptrs(True, 0), tk)
+        ops.v_convert_peers(v[0, give:give + main], main, vmax, world, v_ptrs(0), d * world * m, world * m, v_scale)
+    if edge > 0:
+        for i, x in enumerate((q, k, v)):
+            if keep > main:
+                stage[i, :keep - main].copy_(x[0, give + main:])
+    for w in works:
+        w.wait()
+    if edge > 0:
+        ops.quant_rows_peers(stage[0], edge, None, False, world, code_ptrs(False, main), d, row, scale_ptrs(False, mq), tq)
+        ops.quant_rows_peers(stage[1], edge, km, True, world, code_ptrs(True, main), d, row, scale_ptrs(True, mk), tk)
+        ops.v_convert_peers(stage[2], edge, vmax, world, v_ptrs(main), d * world * m, world * m, v_scale)
+    hdl.barrier()      # all stores of all ranks have landed
+
+    qk = hdl.get_buffer(rank, (1, world * m, 2, hp, d), torch.int8, 0)
+    v8 = hdl.get_buffer(rank, (hp, d, world * m), torch.uint8, off_v)
+    q_scale = hdl.get_buffer(rank, (1, hp, tq), torch.float32, off_qs // 4)
+    k_scale = hdl.get_buffer(rank, (1, hp, tk), torch.float32, off_ks // 4)
+    if sm_scale is None:
+        sm_scale = d ** -0.5
+    o = ops.attention(qk[:, :total, 0], qk[:, :total, 1], v8, q_scale, k_scale,
+                      v_scale[rank * hp:(rank + 1) * hp].contiguous(), dt, is_causal, sm_scale)
+    r_ = _a2a_heads_out(o, group, world)
+    out = torch.empty((1, n, h, d), dtype=dt, device=dev)
+    out.view(n, world, hp, d).copy_(r_.transpose(0, 1))
+    return out
+
+
 def ulysses_sageattn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, group=None,
                      attn_fn: Optional[Callable] = None, head_chunks: int = 1, transport: str = "nccl",
                      comm_sms: int = 0, payload: str = "16bit", _q8_ops=None, **kwargs) -> torch.Tensor:
@@ -490,7 +616,9 @@ def ulysses_sageattn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, group=No
     NCCL's all-to-all kernels (which need SMs) really run next to the attention of another group.
     `payload`: "16bit" ships q, k, v as they are and quantises after the all-to-all; "int8" (B = 1 self-attention with
     head_dim 64 / 128 through the default `sageattn`) quantises the sequence shards first and ships INT8 / e4m3 codes
-    and scales - half the inbound bytes (see _ulysses_b1_q8); shapes it does not cover fall back to "16bit"."""
+    and scales - half the inbound bytes (see _ulysses_b1_q8); shapes it does not cover fall back to "16bit".  With
+    `transport="p2p"` the quantisers store straight into the peers' symmetric-memory arenas and there is no inbound
+    collective at all (_ulysses_b1_q8_p2p)."""
     if kwargs.pop("return_lse", False):
         raise ValueError("ulysses_sageattn does not return the LSE")
     kwargs.pop("tensor_layout", None)
@@ -510,7 +638,8 @@ def ulysses_sageattn(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, group=No
             (_q8_ops is not None or (default_attn and q.is_cuda and set(kwargs) <= {"is_causal", "sm_scale", "smooth_k"}
                                      and kwargs.get("smooth_k", True))):
         ops = _q8_ops if _q8_ops is not None else _Q8CudaOps()
-        return _ulysses_b1_q8(q, k, v, group, world, ops, bool(kwargs.get("is_causal", False)), kwargs.get("sm_scale"))
+        fn = _ulysses_b1_q8_p2p if transport == "p2p" and q.is_cuda and world <= 16 else _ulysses_b1_q8
+        return fn(q, k, v, group, world, ops, bool(kwargs.get("is_causal", False)), kwargs.get("sm_scale"))
     if q.size(0) == 1 and k.size(0) == 1 and all(t.is_contiguous() for t in (q, k, v)):
         # the DiT case (B = 1): communication pipelined against attention over groups of heads
         if transport == "p2p" and (k.size(1) != q.size(1) or v.size(1) != k.size(1)):

@@ -131,6 +131,20 @@ def test_q8_device_half_matches_one_gpu_quantisers(n, d):
     ops.quant_rows(stage[1], cut, km, True, world, send2[:, :cut, 1], ks2[:, :, :ck])
     ops.quant_rows(stage[1, cut:], n - cut, km, True, world, send2[:, cut:, 1], ks2[:, :, ck:ck + ek])
     assert torch.equal(send2[:, :n], send[:, :n]) and torch.equal(qs2, qs) and torch.equal(ks2, ks)
+    # the same through one base pointer per destination (here: separate local tensors; on several GPUs the peers'
+    # symmetric-memory arenas), scales at a column offset of a wider per-head row, guard entries untouched
+    dst = [torch.zeros((m, 2, hp, d), dtype=torch.int8, device="cuda") for _ in range(world)]
+    wide_q = [torch.full((hp, nsq + 40), -7.0, device="cuda") for _ in range(world)]
+    wide_k = [torch.full((hp, nsk + 12), -7.0, device="cuda") for _ in range(world)]
+    ops.quant_rows_peers(stage[0], n, None, False, world, [t.data_ptr() for t in dst], d, 2 * hp * d,
+                         [t.data_ptr() + 8 * 4 for t in wide_q], nsq + 40)
+    ops.quant_rows_peers(stage[1], n, km, True, world, [t.data_ptr() + hp * d for t in dst], d, 2 * hp * d,
+                         [t.data_ptr() + 4 * 4 for t in wide_k], nsk + 12)
+    for p in range(world):
+        assert torch.equal(dst[p][:n], send[p, :n])
+        assert torch.equal(wide_q[p][:, 8:8 + nsq], qs[p]) and torch.equal(wide_k[p][:, 4:4 + nsk], ks[p])
+        assert (wide_q[p][:, :8] == -7).all() and (wide_q[p][:, 8 + nsq:] == -7).all()
+        assert (wide_k[p][:, :4] == -7).all() and (wide_k[p][:, 4 + nsk:] == -7).all()
     # V: conversion with a caller-provided range == the one-GPU per_channel_fp8 (codes, scales; padding zeroed)
     v8 = torch.full((world, hp, d, m), 0x7F, dtype=torch.uint8, device="cuda")
     v_scale = torch.empty((h, d), device="cuda")
@@ -144,6 +158,12 @@ def test_q8_device_half_matches_one_gpu_quantisers(n, d):
     ops.v_convert(stage[2], cut, st[1], world, v8b[..., :cut], v_scale)
     ops.v_convert(stage[2, cut:], n - cut, st[1], world, v8b[..., cut:], v_scale)
     assert torch.equal(v8b[..., :npad], v8[..., :npad])
+    vdst = [torch.full((hp, d, 2 * m), 0x7F, dtype=torch.uint8, device="cuda") for _ in range(world)]
+    v_scale2 = torch.empty_like(v_scale)
+    ops.v_convert_peers(stage[2], n, st[1], world, [t.data_ptr() + m for t in vdst], d * 2 * m, 2 * m, v_scale2)
+    for p in range(world):
+        assert torch.equal(vdst[p][..., m:m + npad], v8[p][..., :npad]) and (vdst[p][..., :m] == 0x7F).all()
+    assert torch.equal(v_scale2, v_scale)
     # the attention kernel on those buffers as the receiving rank sees them == the operator's own two-call path
     from sageattention_b200 import _lib, core
     o_ref = torch.empty((1, n, h, d), dtype=q.dtype, device="cuda")
@@ -169,7 +189,13 @@ def _q8_worker(rank, world, port, n, h, d, causal, q_out):
         args = (q[:, sl].contiguous(), k[:, sl].contiguous(), v[:, sl].contiguous())
         o = parallel.ulysses_sageattn(*args, payload="int8", is_causal=causal)
         o2 = parallel.ulysses_sageattn(*args, payload="int8", is_causal=causal)     # buffers of a second call
+        # the same with the quantisers storing into the peers' symmetric-memory arenas (no inbound collective): three
+        # calls in a row (the arena is reused), the second on other data
+        o3 = parallel.ulysses_sageattn(*args, payload="int8", transport="p2p", is_causal=causal)
+        parallel.ulysses_sageattn(args[1], args[2], args[0], payload="int8", transport="p2p", is_causal=causal)
+        o4 = parallel.ulysses_sageattn(*args, payload="int8", transport="p2p", is_causal=causal)
         torch.cuda.synchronize()
+        o2 = o2 if (torch.equal(o3, o) and torch.equal(o4, o)) else o2 + 1   # any difference fails `repeat_same` below
         ref = torch.nn.functional.scaled_dot_product_attention(
             q.float().transpose(1, 2), k.float().transpose(1, 2), v.float().transpose(1, 2),
             is_causal=causal).transpose(1, 2)[:, sl]
