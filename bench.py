@@ -328,7 +328,7 @@ def run_sp(dev, world, rank, barrier, max_over_ranks, transport="nccl", chunks=1
     # scales through the inbound all-to-alls (1 byte per element instead of 2), 16-bit output back
     try:
         class _NullAttention(parallel._Q8CudaOps):
-            def attention(self, q8, k8, v8, q_scale, k_scale, v_scale, out_dtype, is_causal, sm_scale):
+            def attention(self, q8, k8, v8, q_scale, k_scale, v_scale, out_dtype, is_causal, sm_scale, o_peers=None):
                 return torch.empty((1, q8.size(1), q8.size(2), q8.size(3)), dtype=out_dtype, device=q8.device)
         full8 = lambda: parallel.ulysses_sageattn(qs, ks_, vs_, payload="int8", is_causal=False)
         comm8 = lambda: parallel.ulysses_sageattn(qs, ks_, vs_, payload="int8", _q8_ops=_NullAttention(), is_causal=False)
@@ -355,8 +355,9 @@ def run_sp(dev, world, rank, barrier, max_over_ranks, transport="nccl", chunks=1
             "ms": round(ms9, 3), "tops": round(flops / (ms9 * 1e-3) * 1e-12, 1),
             "comm_and_prepass_ms": round(comm9_ms, 3), "efficiency": round(one_ms / (world * ms9), 4),
             "note": "quantiser launches write INT8 / e4m3 codes and scales into the destination ranks' arenas (one base "
-                    "pointer per destination); two signal-pad barriers; statistics all-gather, halo and the 16-bit way "
-                    "back over NCCL"}
+                    "pointer per destination) and the attention kernel's TMA-store epilogue writes every destination's "
+                    "output rows into its arena; three signal-pad barriers; only the statistics all-gather and the "
+                    "halo go through NCCL"}
     except Exception as e:
         rec["int8_payload_peer_stores"] = {"error": f"{type(e).__name__}: {e}"[:300]}
     return rec

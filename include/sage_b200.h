@@ -246,6 +246,18 @@ typedef struct sage_attn_args {
   const int* cu_seqlens_q; const int* cu_seqlens_k; const int* cu_seqlens_q_scale; const int* cu_seqlens_k_scale;
   const int* cu_pairs;
   int nseq;
+  /* Sequence-parallel output scatter (no counterpart in the reference; B = 1, fixed length).  NULL o_peer_ptrs = all of O
+     goes to `o`.  Otherwise rows [s * o_peer_rows, (s + 1) * o_peer_rows) of O are stored to o_peer_ptrs[s] (HOST array of
+     o_peer_count <= 16 device pointers, normally the destination ranks' symmetric-memory output buffers, reached over
+     NVLink) as [o_peer_rows, Hq, D] with the given element strides - the kernel's TMA-store epilogue is the way back of
+     the Ulysses all-to-all (a tile whose rows belong to two destinations is stored row by row).  o_peer_maps: device
+     scratch of SAGE_O_PEER_SCRATCH_BYTES, 64-byte aligned, which the call fills (on the stream) with the destinations'
+     tensor maps and addresses; it must stay untouched until the kernel has finished; `o` must still be a valid tensor. */
+#define SAGE_O_PEER_SCRATCH_BYTES (16 * 128 + 16 * 8)
+  void* const* o_peer_ptrs;
+  int o_peer_count, o_peer_rows;
+  int64_t o_peer_stride_h, o_peer_stride_n;
+  void* o_peer_maps;
 } sage_attn_args;
 
 int sage_attn_i8_f16(const sage_attn_args* a, void* stream);

@@ -32,6 +32,8 @@ class AttnArgs(ctypes.Structure):
         ("mask", c_vp), ("mask_kind", c_int), ("mask_stride_b", c_i64), ("mask_stride_h", c_i64), ("mask_stride_m", c_i64),
         ("cu_seqlens_q", c_vp), ("cu_seqlens_k", c_vp), ("cu_seqlens_q_scale", c_vp), ("cu_seqlens_k_scale", c_vp),
         ("cu_pairs", c_vp), ("nseq", c_int),
+        ("o_peer_ptrs", ctypes.POINTER(c_vp)), ("o_peer_count", c_int), ("o_peer_rows", c_int),
+        ("o_peer_stride_h", c_i64), ("o_peer_stride_n", c_i64), ("o_peer_maps", c_vp),
     ]
 
 

@@ -11,6 +11,8 @@ and no CPU fallback: a CPU tensor or a missing library raises.
 import warnings
 from typing import Any, Optional
 
+import ctypes
+
 import torch
 
 from . import _lib
@@ -130,7 +132,7 @@ def _prepare_mask(attn_mask, q, b, hq, nq, nk):
 
 
 def _launch(fp8, q_int8, k_int8, v, o, q_scale, k_scale, v_scale, v_mean, tensor_layout, is_causal, gran,
-            warp_q, sm_scale, return_lse, npad_v=0, debug_s=None, mask=None, varlen=None):
+            warp_q, sm_scale, return_lse, npad_v=0, debug_s=None, mask=None, varlen=None, o_peers=None):
     """One call into sage_attn_i8_f8 / sage_attn_i8_f16; returns the base-2 LSE or None."""
     lib = _lib.load()
     b, hq, nq, d, q4 = _dims(q_int8, tensor_layout)
@@ -170,6 +172,15 @@ def _launch(fp8, q_int8, k_int8, v, o, q_scale, k_scale, v_scale, v_mean, tensor
         a.cu_seqlens_q, a.cu_seqlens_k = cu_q.data_ptr(), cu_k.data_ptr()
         a.cu_seqlens_q_scale, a.cu_seqlens_k_scale, a.cu_pairs = cu_qs.data_ptr(), cu_ks.data_ptr(), cu_pairs.data_ptr()
         a.nseq = cu_q.numel() - 1
+    if o_peers is not None:
+        # sequence-parallel output scatter: (addresses of the destinations' output rows, rows per destination,
+        # head stride, row stride, device scratch for the tensor maps) - include/sage_b200.h, o_peer_*
+        ptrs, rows, stride_h, stride_n, scratch = o_peers
+        arr = (ctypes.c_void_p * len(ptrs))(*ptrs)
+        a.o_peer_ptrs = ctypes.cast(arr, ctypes.POINTER(ctypes.c_void_p))
+        a.o_peer_count, a.o_peer_rows = len(ptrs), rows
+        a.o_peer_stride_h, a.o_peer_stride_n = stride_h, stride_n
+        a.o_peer_maps = scratch.data_ptr()
     fn = lib.sage_attn_i8_f8 if fp8 else lib.sage_attn_i8_f16
     with _on_device(o.device):
         if KERNEL_EVENTS is not None:

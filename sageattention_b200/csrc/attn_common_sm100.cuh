@@ -77,6 +77,14 @@ struct AttnKernelParams {
   // cu_*_scale[s], cu_pairs = prefix of ceil(q_len / 256) (all written by sage_quant_per_block_varlen_int8)
   const int* cu_q; const int* cu_k; const int* cu_q_scale; const int* cu_k_scale; const int* cu_pairs;
   int nseq;
+  // sequence-parallel output scatter (sage_attn_args.o_peer_*): rows [s * o_peer_rows, (s + 1) * o_peer_rows) of O go
+  // through tensor map o_peer_maps[s] (in global memory; it describes destination rank s's output rows for this
+  // rank's heads, usually in s's symmetric memory over NVLink) instead of tmO - the epilogue is the way back of the
+  // all-to-all.  Null = everything through tmO.
+  const CUtensorMap* o_peer_maps;
+  void* const* o_peer_ptrs;                      // the destinations' base addresses (device array, behind the maps)
+  long long o_peer_stride_h, o_peer_stride_n;    // elements
+  int o_peer_rows, o_peer_count;
 };
 
 // Token offsets and lengths of the sequence a work item belongs to (the whole tensor when not packed).
@@ -404,6 +412,27 @@ __device__ __forceinline__ void softmax_epilogue(const AttnKernelParams& p, int 
     case 6: epilogue_convert<D, true, true, false>(oall, inv_d, vs_addr, vmp, orow, ox); break;
     default: epilogue_convert<D, true, true, true>(oall, inv_d, vs_addr, vmp, orow, ox); break;
   }
+  // sequence-parallel output scatter: a tile whose rows belong to TWO destination ranks goes out row by row (a bulk
+  // tensor store cannot start at a negative row of the second destination's map: illegal instruction, measured)
+  bool straddle = false;
+  int peer0 = 0;
+  if constexpr (!kVarlen) {
+    if (p.o_peer_maps != nullptr) {
+      peer0 = q_tile_start / p.o_peer_rows;
+      straddle = (min(q_tile_start + kTileQ, p.Nq) - 1) / p.o_peer_rows != peer0;
+      if (straddle && q_row < p.Nq) {
+        const int s_ = q_row / p.o_peer_rows;
+        uint8_t* dst = reinterpret_cast<uint8_t*>(p.o_peer_ptrs[s_]) +
+                       ((long long)(q_row - s_ * p.o_peer_rows) * p.o_peer_stride_n + (long long)h * p.o_peer_stride_h) * 2;
+#pragma unroll
+        for (int c0 = 0; c0 < D; c0 += 8) {
+          const uint32_t chunk = (uint32_t)((c0 & 63) >> 3);
+          const int4 v = ld_shared_v4(orow + (uint32_t)(c0 >> 6) * (kTileQ * 128) + ((chunk ^ ox) << 4));
+          *reinterpret_cast<int4*>(dst + c0 * 2) = v;
+        }
+      }
+    }
+  }
   if constexpr (kVarlen) {
     if (rows_valid < kTileQ) {
       // last tile of a sequence: a bulk tensor store would run into the next sequence's rows, so every thread
@@ -422,10 +451,19 @@ __device__ __forceinline__ void softmax_epilogue(const AttnKernelParams& p, int 
   }
   fence_proxy_async_smem();
   named_bar_sync(3 + t, kTileQ);
-  if (row == 0 && (!kVarlen || rows_valid >= kTileQ)) {
+  if (row == 0 && (!kVarlen || rows_valid >= kTileQ) && !straddle) {
+    if (!kVarlen && p.o_peer_maps != nullptr) {
+      // all of the tile's rows (< Nq) belong to destination peer0: its map clips the rows beyond its o_peer_rows
+      if (peer0 < p.o_peer_count) {
 #pragma unroll
-    for (int c = 0; c < D / 64; ++c)
-      tma_store_4d(tmO, o_smem + c * (kTileQ * 128), c * 64, q_off + q_tile_start, h, kVarlen ? 0 : b);
+        for (int c = 0; c < D / 64; ++c)
+          tma_store_4d(p.o_peer_maps + peer0, o_smem + c * (kTileQ * 128), c * 64, q_tile_start - peer0 * p.o_peer_rows, h, 0);
+      }
+    } else {
+#pragma unroll
+      for (int c = 0; c < D / 64; ++c)
+        tma_store_4d(tmO, o_smem + c * (kTileQ * 128), c * 64, q_off + q_tile_start, h, kVarlen ? 0 : b);
+    }
     tma_store_commit();
   }
   const bool store = q_row < p.Nq;

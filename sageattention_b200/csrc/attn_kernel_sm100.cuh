@@ -1011,6 +1011,40 @@ static int launch_attn(const sage_attn_args* a, cudaStream_t stream) {
   SAGE_REQUIRE(kVarlen == (a->cu_seqlens_q != nullptr), "internal: varlen kernel selection");
   p.cu_q = a->cu_seqlens_q; p.cu_k = a->cu_seqlens_k; p.cu_q_scale = a->cu_seqlens_q_scale;
   p.cu_k_scale = a->cu_seqlens_k_scale; p.cu_pairs = a->cu_pairs; p.nseq = a->nseq;
+  p.o_peer_maps = nullptr;
+  p.o_peer_ptrs = nullptr;
+  p.o_peer_stride_h = p.o_peer_stride_n = 0;
+  p.o_peer_rows = p.o_peer_count = 0;
+  if (a->o_peer_ptrs != nullptr) {
+    SAGE_REQUIRE(!kVarlen && a->B == 1, "o_peer_ptrs: fixed-length calls with B = 1 only");
+    SAGE_REQUIRE(a->o_peer_count > 0 && a->o_peer_count <= 16 && a->o_peer_rows > 0 && a->o_peer_maps != nullptr &&
+                 (reinterpret_cast<uintptr_t>(a->o_peer_maps) & 63) == 0,
+                 "o_peer_*: 1..16 destinations, rows per destination > 0, a 64-byte aligned device scratch of SAGE_O_PEER_SCRATCH_BYTES");
+    SAGE_REQUIRE((long long)a->o_peer_count * a->o_peer_rows >= a->Nq, "o_peer_count * o_peer_rows (%d * %d) < Nq (%d)",
+                 a->o_peer_count, a->o_peer_rows, a->Nq);
+    // scratch layout: the tensor maps (128 bytes each), then the base addresses
+    struct alignas(64) { CUtensorMap maps[16]; void* ptrs[16]; } host;
+    CUtensorMap* host_maps = host.maps;
+    for (int s_ = 0; s_ < a->o_peer_count; ++s_) {
+      host.ptrs[s_] = a->o_peer_ptrs[s_];
+      rc = make_map4(&host_maps[s_], CU_TENSOR_MAP_DATA_TYPE_UINT16, a->o_peer_ptrs[s_], d_og, a->o_peer_rows, a->Hq, 1,
+                     a->o_peer_stride_n * 2, a->o_peer_stride_h * 2,
+                     (uint64_t)a->o_peer_stride_n * 2 * (uint64_t)a->o_peer_rows, 64, kTileQ, CU_TENSOR_MAP_SWIZZLE_128B,
+                     "o_peer");
+      if (rc) return rc;
+    }
+    // (pageable source: staged before the call returns)
+    SAGE_CUDA(cudaMemcpyAsync(a->o_peer_maps, host_maps, sizeof(CUtensorMap) * a->o_peer_count, cudaMemcpyHostToDevice,
+                              stream));
+    void* dev_ptrs = reinterpret_cast<uint8_t*>(a->o_peer_maps) + sizeof(CUtensorMap) * 16;
+    SAGE_CUDA(cudaMemcpyAsync(dev_ptrs, host.ptrs, sizeof(void*) * a->o_peer_count, cudaMemcpyHostToDevice, stream));
+    p.o_peer_maps = reinterpret_cast<const CUtensorMap*>(a->o_peer_maps);
+    p.o_peer_ptrs = reinterpret_cast<void* const*>(dev_ptrs);
+    p.o_peer_stride_h = a->o_peer_stride_h;
+    p.o_peer_stride_n = a->o_peer_stride_n;
+    p.o_peer_rows = a->o_peer_rows;
+    p.o_peer_count = a->o_peer_count;
+  }
   auto kern = sage_attn_fwd_kernel<D, kFp8, kMask, kVarlen>;
   // per template instantiation AND per device: function attributes belong to the device's context
   static SmemAttrOnce smem_attr;

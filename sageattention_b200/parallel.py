@@ -368,14 +368,16 @@ class _Q8CudaOps:
                                                         v_scale.data_ptr(), world, hp, rows, n_stat, d, _dtype_code(x),
                                                         self.scale_max, _stream(x)))
 
-    def attention(self, q8, k8, v8, q_scale, k_scale, v_scale, out_dtype, is_causal, sm_scale):
-        """q8 / k8: int8 [1, N, h, D] (strided), v8: uint8 [h, D, Npad]; -> o [1, N, h, D]."""
+    def attention(self, q8, k8, v8, q_scale, k_scale, v_scale, out_dtype, is_causal, sm_scale, o_peers=None):
+        """q8 / k8: int8 [1, N, h, D] (strided), v8: uint8 [h, D, Npad]; -> o [1, N, h, D].  With `o_peers` (see
+        core._launch) the rows go to the destination ranks' buffers instead and `o` is a one-tile dummy."""
         from . import _lib, core
         _, n, h, d = q8.shape
-        o = torch.empty((1, n, h, d), dtype=out_dtype, device=q8.device)
+        # (with o_peers nothing is stored through `o`: its tensor map only has to be constructible)
+        o = torch.empty((1, n if o_peers is None else 128, h, d), dtype=out_dtype, device=q8.device)
         v4 = v8.view(torch.float8_e4m3fn).unsqueeze(0).transpose(1, 2)   # "NHD" form of v_fp8: [B, D, H, Npad]
         core._launch(True, q8, k8, v4, o, q_scale, k_scale, v_scale, None, "NHD", is_causal, _lib.GRAN_PER_THREAD, 32,
-                     sm_scale, False)
+                     sm_scale, False, o_peers=o_peers)
         return o
 
 
@@ -507,13 +509,15 @@ def _ulysses_b1_q8(q, k, v, group, world, ops, is_causal=False, sm_scale=None):
     return out
 
 
-def _ulysses_b1_q8_p2p(q, k, v, group, world, ops, is_causal=False, sm_scale=None):
+def _ulysses_b1_q8_p2p(q, k, v, group, world, ops, is_causal=False, sm_scale=None, peer_out=True):
     """_ulysses_b1_q8 with NO inbound collective: every rank owns a symmetric-memory arena laid out as the attention
     kernel wants its inputs ([P, M, 2, H/P, D] Q / K codes by source rank, V^T [H/P, D, P*M], scales [H/P, entries]), and
     the quantisers of every rank store their codes and scales straight into the destinations' arenas over NVLink
     (sage_quant_per_thread_int8_peers / sage_v_fp8_from_absmax_peers: one base pointer per destination) - the launch is
     quantiser and all-to-all in one.  Two signal-pad barriers frame the stores (everybody has finished reading the
-    previous call's arena / everything has landed).  Statistics all-gather, halo and the way back as in _ulysses_b1_q8."""
+    previous call's arena / everything has landed).  `peer_out`: the way back goes through the attention kernel's
+    epilogue as well (sage_attn_args.o_peer_*: rows of destination s are TMA-stored into s's arena), so the only NCCL
+    traffic left is the small statistics all-gather and the halo; False = 16-bit output through NCCL as in _ulysses_b1_q8."""
     group = group if group is not None else dist.group.WORLD
     rank = dist.get_rank(group)
     _, n, h, d = q.shape
@@ -529,7 +533,9 @@ def _ulysses_b1_q8_p2p(q, k, v, group, world, ops, is_causal=False, sm_scale=Non
     off_v = al(world * m * 2 * hp * d)
     off_qs = off_v + al(hp * d * world * m)
     off_ks = off_qs + al(hp * tq * 4)
-    nbytes = off_ks + al(hp * tk * 4)
+    off_o = off_ks + al(hp * tk * 4)               # this rank's output rows, [n, H, D], written by every rank's epilogue
+    es = q.element_size()
+    nbytes = off_o + al(n * h * d * es) if peer_out else off_o
     hdl, _ = _arena(nbytes, dev, group)
     base = [hdl.get_buffer(p, (nbytes,), torch.uint8, 0).data_ptr() for p in range(world)]
 
@@ -592,6 +598,15 @@ def _ulysses_b1_q8_p2p(q, k, v, group, world, ops, is_causal=False, sm_scale=Non
     k_scale = hdl.get_buffer(rank, (1, hp, tk), torch.float32, off_ks // 4)
     if sm_scale is None:
         sm_scale = d ** -0.5
+    if peer_out:
+        # the way back inside the attention kernel: its TMA-store epilogue writes the rows of destination rank s (this
+        # rank's heads) straight into s's [n, H, D] output region over NVLink; a third barrier, one local copy out
+        scratch = torch.empty(16 * 136, dtype=torch.uint8, device=dev)     # SAGE_O_PEER_SCRATCH_BYTES
+        o_peers = ([b_ + off_o + rank * hp * d * es for b_ in base], n, d, h * d, scratch)
+        ops.attention(qk[:, :total, 0], qk[:, :total, 1], v8, q_scale, k_scale,
+                      v_scale[rank * hp:(rank + 1) * hp].contiguous(), dt, is_causal, sm_scale, o_peers=o_peers)
+        hdl.barrier()  # every rank's epilogue stores have landed
+        return hdl.get_buffer(rank, (1, n, h, d), dt, off_o // es).clone()
     o = ops.attention(qk[:, :total, 0], qk[:, :total, 1], v8, q_scale, k_scale,
                       v_scale[rank * hp:(rank + 1) * hp].contiguous(), dt, is_causal, sm_scale)
     r_ = _a2a_heads_out(o, group, world)

@@ -173,6 +173,19 @@ def test_q8_device_half_matches_one_gpu_quantisers(n, d):
         o = ops.attention(send[p:p + 1, :n, 0], send[p:p + 1, :n, 1], v8[p], qs[p:p + 1], ks[p:p + 1],
                           v_scale[p * hp:(p + 1) * hp].contiguous(), q.dtype, False, d ** -0.5)
         assert torch.equal(o, o_ref[:, :, p * hp:(p + 1) * hp])
+    # the output scattered by the kernel's epilogue (sage_attn_args.o_peer_*): rows [s * 400, (s + 1) * 400) of every head
+    # group go to destination s's [400, H, D] buffer (here local tensors; tiles straddle the boundaries, the last
+    # destination is only partly filled)
+    rows = 400
+    dests = [torch.full((rows, h, d), 7.0, dtype=q.dtype, device="cuda") for _ in range(3)]
+    scratch = torch.empty(16 * 136, dtype=torch.uint8, device="cuda")     # SAGE_O_PEER_SCRATCH_BYTES
+    for p in range(world):
+        ops.attention(send[p:p + 1, :n, 0], send[p:p + 1, :n, 1], v8[p], qs[p:p + 1], ks[p:p + 1],
+                      v_scale[p * hp:(p + 1) * hp].contiguous(), q.dtype, False, d ** -0.5,
+                      o_peers=([t.data_ptr() + p * hp * d * 2 for t in dests], rows, d, h * d, scratch))
+        torch.cuda.synchronize()
+    got = torch.cat(dests)
+    assert torch.equal(got[:n], o_ref[0])
 
 
 def _q8_worker(rank, world, port, n, h, d, causal, q_out):
