@@ -360,6 +360,12 @@ def run_sp(dev, world, rank, barrier, max_over_ranks, transport="nccl", chunks=1
                     "halo go through NCCL"}
     except Exception as e:
         rec["int8_payload_peer_stores"] = {"error": f"{type(e).__name__}: {e}"[:300]}
+    cands = [("16-bit payload, NCCL all-to-alls (ulysses_sageattn defaults)", rec["ms"], rec["efficiency"])]
+    for key, label in (("int8_payload", 'payload="int8"'), ("int8_payload_peer_stores", 'payload="int8", transport="p2p"')):
+        if "ms" in rec.get(key, {}):
+            cands.append((label, rec[key]["ms"], rec[key]["efficiency"]))
+    best = min(cands, key=lambda c: c[1])
+    rec["best"] = {"variant": best[0], "ms": best[1], "efficiency": best[2]}
     return rec
 
 
