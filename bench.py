@@ -405,17 +405,21 @@ def run_reference(args):
         return
     steps = max(1, args.steps)
     tops_l, sample, ts = [], "", []
-    for i in range(args.warmup + steps):
-        tops, sample, t = cpu_sample(api, b, h, n, d, causal, dtype_name, budget_s=8.0)
-        if i >= args.warmup:
+    # every step is a bounded sample (about 4 s of CPU work); the whole arm stops after about two minutes of wall time
+    # whatever --steps says (the default of the GPU arm is 400), and reports how many steps it timed
+    t_wall = time.time()
+    warm = min(args.warmup, 2)
+    for i in range(warm + steps):
+        tops, sample, t = cpu_sample(api, b, h, n, d, causal, dtype_name, budget_s=4.0)
+        if i >= warm:
             tops_l.append(tops)
             ts.append(t)
-        if sum(ts) > 150:
+        if time.time() - t_wall > 120 and tops_l:
             break
     val = statistics.mean(tops_l)
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": "TOPS", "n_gpus": args.gpus,
-        "steps": len(tops_l), "warmup": args.warmup, "ms_per_step": statistics.mean(ts) * 1e3,
+        "steps": len(tops_l), "warmup": warm, "ms_per_step": statistics.mean(ts) * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "int8+fp16" if "fp16" in api else "int8+fp8",
         "data": "synthetic",
         "config": {"workload": workload_string(args.workload)},
