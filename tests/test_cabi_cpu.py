@@ -55,6 +55,19 @@ def test_argument_validation_without_gpu():
     rc = lib.sage_prepass_qkv_fp8(t, t, t, t, 16, 16, 16, t, 16, 0, 0, 0, 16, 1, 1, 1, 64, 64, 64, 64, 0, 1, 32, 16, 4,
                                   448.0, 72, None)
     assert rc < 0 and b"d_og" in lib.sage_last_error()
+    # the sequence-parallel entry points: destination tables of at most 16 ranks, scale rows wide enough for the call's
+    # own entries, a scratch buffer for the output maps - all rejected before any CUDA call
+    ptrs = (ctypes.c_void_p * 17)(*([4096] * 17))
+    rc = lib.sage_quant_per_thread_int8_peers(t, None, ptrs, 128, 256, ptrs, 17, 1, 64, 128, 0, 0, 32, 64, None)
+    assert rc < 0 and b"16" in lib.sage_last_error()
+    rc = lib.sage_quant_per_thread_int8_peers(t, None, ptrs, 128, 256, ptrs, 2, 1, 256, 128, 0, 1, 64, 8, None)
+    assert rc < 0 and b"scale_per_bh" in lib.sage_last_error()
+    rc = lib.sage_quant_per_thread_int8_strided(t, None, t, 16, 1, 1, 256, 128, 0, 0, 32, 32, None)
+    assert rc < 0 and b"scale_per_bh" in lib.sage_last_error()
+    rc = lib.sage_v_fp8_from_absmax_peers(t, ptrs, 128, 100, 16, None, 2, 1, 64, 64, 128, 0, 448.0, None)
+    assert rc < 0 and b"16-byte" in lib.sage_last_error()
+    rc = lib.sage_col_sum_absmax(t, None, None, 1, 1, 64, 128, 0, 16, None)
+    assert rc < 0 and b"null" in lib.sage_last_error()
     with pytest.raises(ValueError):
         _lib.check(-1)
 
