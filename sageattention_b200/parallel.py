@@ -168,6 +168,7 @@ def _ulysses_b1(q, k, v, group, world, attn_fn, head_chunks, kwargs):
 # arenas with contiguous device-to-device copies, which the copy engines execute - no SM needed - and a
 # signal-pad barrier tells the receivers that everything has landed.
 _ARENAS = {}
+_ARENAS_RETIRED = []
 
 
 def _arena(nbytes: int, device: torch.device, group):
@@ -177,6 +178,10 @@ def _arena(nbytes: int, device: torch.device, group):
     key = (device.index, group.group_name)
     cur = _ARENAS.get(key)
     if cur is None or cur[1] < nbytes:
+        if cur is not None:
+            # kernels of the previous call (here or on a peer) may still be reading / writing the old arena: it is kept
+            # alive instead of being unmapped under them (growth is rare: the size is a function of the call's shapes)
+            _ARENAS_RETIRED.append(cur)
         cap = max(nbytes, 1 << 20)
         buf = symm.empty(cap, dtype=torch.uint8, device=device)
         cur = (symm.rendezvous(buf, group), cap, buf)
