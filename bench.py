@@ -48,10 +48,11 @@ WORKLOADS = {
     "wan": ("sageattn", 1, 40, 75600, 128, False, "bfloat16"),
 }
 # dram__bytes_read.sum + dram__bytes_write.sum of the attention kernel, one `ncu --set full` capture
-# per workload (profiles/r2_ncu_attn_summary.txt, round 2); algorithmic bytes at C2 fp16 = 402.7e6
-NCU_TRAFFIC = {"c2_fp16": 379.21e6, "c3_fp8": 305.84e6}
-NCU_TRAFFIC_SOURCE = {"c2_fp16": "ncu capture profiles/r2_ncu_attn_summary.txt, round 2 (not measured in this run)",
-                      "c3_fp8": "ncu capture profiles/r2_ncu_attn_summary.txt, round 2 (not measured in this run)"}
+# per workload of the current (unified) kernel (profiles/r2n_ncu_attn_summary.txt, end of round 2); algorithmic bytes at
+# C2 fp16 = 402.7e6
+NCU_TRAFFIC = {"c2_fp16": 376.61e6, "c3_fp8": 305.46e6}
+NCU_TRAFFIC_SOURCE = {"c2_fp16": "ncu capture profiles/r2n_ncu_attn_summary.txt, round 2 (not measured in this run)",
+                      "c3_fp8": "ncu capture profiles/r2n_ncu_attn_summary.txt, round 2 (not measured in this run)"}
 METRIC = "attention TOPS @hd64/hd128 seq 1K-32K (causal/non-causal), % of INT8/FP8 tensor peak"
 
 
