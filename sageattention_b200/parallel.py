@@ -11,6 +11,12 @@ operator is independent, so two layouts cover the named DiT configs:
   (`head_chunks`; measured neutral with NCCL, whose kernels need the SMs the persistent attention grid
   holds - DESIGN 5).  NCCL over NVLink/NVSwitch on GPUs; the same code runs
   over gloo on CPU tensors for the host-logic tests (with a stand-in attention function).
+* Ulysses with a quantised payload (`payload="int8"`): the pre-pass runs on the sequence shards BEFORE the
+  exchange, INT8 / e4m3 codes and scales travel instead of 16-bit activations, and the receiving rank goes straight into
+  the attention kernel (`_ulysses_b1_q8`, NCCL).  With `transport="p2p"` (`_ulysses_b1_q8_p2p`) there is no collective on
+  the data path at all: the quantiser launches store into the destination ranks' symmetric-memory arenas over NVLink and
+  the attention kernel's TMA-store epilogue scatters the output rows to the ranks that own them (Wan2.1 layer on 8 GPUs:
+  10.5 ms, 0.97 of linear, against 11.2 ms / 0.91 for the 16-bit NCCL path).
 """
 from typing import Callable, Optional
 
