@@ -156,7 +156,41 @@ def _q8_worker(rank, world, port, nl, h, d, q_out):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("world,nl", [(2, 300), (2, 256), (3, 520)])   # ragged shards (halo), aligned shards, 3 ranks
+def _q8_fallback_worker(rank, world, port, q_out):
+    """Shards shorter than the halo they would need: payload="int8" must fall back to the 16-bit exchange."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        g = torch.Generator().manual_seed(2)
+        n, h, d = 80, 4, 64
+        q, k, v = (torch.randn(1, n, h, d, generator=g) for _ in range(3))
+        full = _sdpa_nhd(q, k, v)
+        nl = n // world
+        sl = slice(rank * nl, (rank + 1) * nl)
+        assert parallel.q8_geometry(nl, world) is None
+        o = parallel.ulysses_sageattn(q[:, sl].contiguous(), k[:, sl].contiguous(), v[:, sl].contiguous(),
+                                      attn_fn=_sdpa_nhd, payload="int8", _q8_ops=_OracleOps())
+        q_out.put((rank, (o - full[:, sl]).abs().max().item()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_quantised_payload_falls_back_for_short_shards():
+    ctx = mp.get_context("spawn")
+    q_out = ctx.Queue()
+    port = 33500 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_q8_fallback_worker, args=(r, 2, port, q_out)) for r in range(2)]
+    for p in procs:
+        p.start()
+    res = [q_out.get(timeout=300) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for rank, err in res:
+        assert err < 1e-5, (rank, err)
+
+
+@pytest.mark.parametrize("world,nl", [(2, 300), (2, 256), (3, 520), (4, 500)])   # ragged (halo), aligned, 3 and 4 ranks
 def test_ulysses_quantised_payload_host_logic(world, nl):
     ctx = mp.get_context("spawn")
     q_out = ctx.Queue()
