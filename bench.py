@@ -406,16 +406,17 @@ def run_reference(args):
         return
     steps = max(1, args.steps)
     tops_l, sample, ts = [], "", []
-    # every step is a bounded sample (about 4 s of CPU work); the whole arm stops after about two minutes of wall time
-    # whatever --steps says (the default of the GPU arm is 400), and reports how many steps it timed
+    # every step is a bounded sample (about 3.5 s of CPU work: the driver's --steps 20 --warmup 5 takes 90 s); the arm
+    # stops after about two and a half minutes of wall time whatever --steps says (the GPU arm's default is 400 steps)
+    # and reports how many steps it timed
     t_wall = time.time()
-    warm = min(args.warmup, 2)
+    warm = args.warmup
     for i in range(warm + steps):
         tops, sample, t = cpu_sample(api, b, h, n, d, causal, dtype_name, budget_s=4.0)
         if i >= warm:
             tops_l.append(tops)
             ts.append(t)
-        if time.time() - t_wall > 120 and tops_l:
+        if time.time() - t_wall > 150 and tops_l:
             break
     val = statistics.mean(tops_l)
     line = {
